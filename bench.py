@@ -1,0 +1,289 @@
+#!/usr/bin/env python
+"""bench.py -- word-count input throughput (BASELINE.json metric) on N B200s of one node.
+
+  python bench.py --gpus 1 --steps 5 --warmup 3
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+         --master-port P bench.py --gpus N --steps K --warmup W
+  python bench.py --impl reference ...      (the reference's CPU algorithm on host cores)
+
+A step is one complete word-count job (map -> [shuffle] -> process -> reduce) over the
+rank's shard of synthetic text.  N=1 runs BASELINE.json configs[1] (1 GiB Zipf(1.1), 50 K
+vocabulary); N>1 runs the configs[2] text (Zipf, 1 M vocabulary) at 2 GiB per rank, cut on
+delimiters, so N=8 is the full 16 GiB configuration ("weak" scaling).  One JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "word-count input GB/s (device-timed, max over ranks)"
+GB = 1e9
+FALLBACK_HBM_GBS = 6650.0        # /opt/skills/guides/B200_PROFILING.md fallback
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.gpu, self.rows, self.proc = gpu_index, [], None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([x.strip() for x in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        self.join(timeout=2)
+        sm = sorted(int(r[1]) for r in self.rows if len(r) > 8 and r[1].isdigit())
+        mx = [int(r[2]) for r in self.rows if len(r) > 8 and r[2].isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) > 8:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(self.rows)}
+
+
+def workload(n_gpus):
+    if n_gpus == 1:
+        return "C2", 1 << 30, "C2: 1 GiB synthetic Zipf(s=1.1) English-like text, 50K vocab, word count on 1xB200"
+    return "C3", 2 << 30, ("C3 text (Zipf s=1.1, 1M vocab), 2 GiB per GPU cut on delimiters (N=8 is the 16 GiB config), "
+                           "hash-partitioned NCCL all-to-all shuffle")
+
+
+def cpu_port_rate(sample, threads=1):
+    """GB/s of the oracle's map -> sort -> run-length reduce (the reference's CPU stages) on `sample`."""
+    from oracle import pyoracle
+    t0 = time.perf_counter()
+    r = pyoracle.wordcount(sample, mode="sort", formats=False)
+    dt = time.perf_counter() - t0
+    return len(sample) / dt / GB, dt, r
+
+
+def run_reference(args, rank, world):
+    """The reference's CPU implementation of the path (oracle port: oracle/_ref cannot take more than
+    5 800 lines), one host thread like the reference, on a bounded sample of the same workload."""
+    if rank != 0:
+        return
+    from locust_b200.textgen import TextGen
+    name, nbytes, desc = workload(args.gpus)
+    sample_bytes = args.cpu_sample_mib << 20
+    g = TextGen.config(name, total_bytes=nbytes * (args.gpus if args.gpus > 1 else 1))
+    sample = g.host(sample_bytes)
+    times = []
+    for i in range(args.warmup + args.steps):
+        rate, dt, _ = cpu_port_rate(sample)
+        if i >= args.warmup:
+            times.append(dt)
+    tot = sum(times)
+    value = sample_bytes * len(times) / tot / GB
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": desc},
+            "cpu_baseline": {"value": value, "unit": "GB/s", "cores": 1, "kind": "port",
+                             "sample": "first %d MiB of the workload text; map -> comparison sort of every token "
+                                       "-> run-length reduce (oracle/wordcount_oracle.c), single thread like the "
+                                       "reference" % args.cpu_sample_mib},
+            "e2e": {"value": value, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="locust_b200", choices=["locust_b200", "reference"])
+    ap.add_argument("--mib", type=int, default=0, help="override per-GPU input size (MiB); not the benchmark config")
+    ap.add_argument("--cpu-sample-mib", type=int, default=32)
+    ap.add_argument("--table-log2", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            sys.exit("bench.py --gpus %d must be launched with torch.distributed.run --nproc-per-node %d"
+                     % (args.gpus, args.gpus))
+        sys.exit("WORLD_SIZE=%d does not match --gpus %d" % (world, args.gpus))
+
+    import torch
+    import torch.distributed as dist
+    import locust_b200
+    from locust_b200.textgen import TextGen
+    if not torch.cuda.is_available():
+        sys.exit("bench.py needs a CUDA device: the word-count path has no CPU implementation")
+    locust_b200.load()
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    name, per_gpu, desc = workload(world)
+    if args.mib:
+        per_gpu = args.mib << 20
+        desc += " [size overridden to %d MiB per GPU: NOT the benchmark configuration]" % args.mib
+    total = per_gpu * world
+    gen = TextGen.config(name, total_bytes=total, device=local_rank)
+    text = torch.empty(per_gpu, dtype=torch.uint8, device=dev)
+    gen.fill_device(text, byte_offset=rank * per_gpu)      # blocks end in a delimiter: shard cuts are token boundaries
+    torch.cuda.synchronize()
+
+    stream = torch.cuda.Stream(device=dev)
+    table_log2 = args.table_log2 or (17 if name == "C2" else 22)
+    wc = locust_b200.WordCount(device=local_rank, table_log2=table_log2, stream=stream.cuda_stream)
+    if world > 1:
+        from locust_b200.shuffle import DistributedWordCount
+        job = DistributedWordCount(wc, dist, dev, stream)
+        step = lambda buf: job.run(buf)
+    else:
+        step = lambda buf: wc.run(buf)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(buf, k):
+        """device time of k steps (ms, max over ranks) and the per-step map-kernel times"""
+        map_ms = []
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            for _ in range(k):
+                step(buf)
+                map_ms.append(wc.stage_ms()[0])
+            e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, map_ms
+
+    # ---- device-resident input ("value") ----------------------------------------------
+    with torch.cuda.stream(stream):
+        for _ in range(args.warmup):
+            step(text)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ms, map_ms = timed(text, args.steps)
+    clocks = sampler.stop()
+    st = wc.stats()
+    launches_per_step = st["kernel_launches"]
+    uniq, tokens = st["unique_keys"], st["tokens"]
+    value = total * args.steps / (ms * 1e-3) / GB
+
+    # roofline of the dominant kernel (tokenize_combine, the whole MAP stage of a step)
+    blob, offs, counts, vals = wc.result_arrays()
+    alg_bytes = per_gpu + int(len(blob)) + 8 * int(len(counts))     # N_in + sum(len_k + 8), SURVEY.md 8(d)
+    avg_map_ms = sum(map_ms) / len(map_ms)
+    peak, peak_src = measured_peak()
+    achieved = alg_bytes / (avg_map_ms * 1e-3) / GB
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "map_kernel_traffic.json")
+    if os.path.exists(tp):
+        try:
+            with open(tp) as f:
+                traffic = json.load(f).get("dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+    roofline = {"bound": "hbm", "kernel": "tokenize_combine_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": alg_bytes, "avg_kernel_ms": avg_map_ms,
+                "map_share_of_step": avg_map_ms * args.steps / ms}
+
+    # ---- end to end: pinned host input in, host result out, every step ---------------------
+    host = torch.empty(per_gpu, dtype=torch.uint8, pin_memory=True)
+    host.copy_(text)
+    torch.cuda.synchronize()
+    d2h = int(len(blob)) + 8 * (int(len(offs)) + 2 * int(len(counts)))
+
+    def e2e_step(buf):
+        step(buf)
+        wc.result_arrays()
+
+    e2e_steps = max(2, min(args.steps, 5))
+    with torch.cuda.stream(stream):
+        e2e_step(host)
+    barrier()
+    t0 = time.perf_counter()
+    with torch.cuda.stream(stream):
+        for _ in range(e2e_steps):
+            e2e_step(host)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e = {"value": total * e2e_steps / e2e_s / GB, "unit": "GB/s", "h2d_bytes_per_step": per_gpu,
+           "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+           "note": "locust_map(LOCUST_HOST) from pinned memory, chunked copy overlapped with map; result copied to host"}
+
+    # ---- the reference's CPU algorithm on this box's host cores (rank 0, N=1) -----------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        sample = host[: args.cpu_sample_mib << 20].numpy()
+        rate, dt, r = cpu_port_rate(sample)
+        cpu = {"value": rate, "unit": "GB/s", "cores": 1, "kind": "port",
+               "sample": "first %d MiB of the same text (%.1f s): map -> comparison sort of every token -> run-length "
+                         "reduce, oracle/wordcount_oracle.c, single thread like the reference"
+                         % (args.cpu_sample_mib, dt)}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                "config": {"workload": desc, "bytes_per_gpu": per_gpu, "tokens_per_gpu": tokens if world == 1 else None,
+                           "unique_keys": uniq, "table_log2": table_log2,
+                           "l2": "input per step (%d MiB per GPU) is larger than the 126 MB L2" % (per_gpu >> 20)},
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
+                "gpu_launches": launches_per_step * args.steps, "gpu_launches_per_step": launches_per_step,
+                "stage_ms_last_step": dict(zip(("map", "process", "reduce"), wc.stage_ms()))}
+        print(json.dumps(line), flush=True)
+    wc.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,157 @@
+/*
+ * locust.h -- C ABI of liblocust.so, the B200-native word-count path of
+ * wuyan33/Locust ("MapReduce" binary, map -> process -> reduce).
+ *
+ * The reference has no FFI layer: its operator surface is the stage split inside
+ * main() (MapReduce/src/main.cu:358-532).  Each entry point below names the
+ * reference code it stands in for.  All entry points are plain C: opaque handle,
+ * pointers and sizes, an int status, no C++ types and no exceptions.  Nothing in
+ * here exits the process; nothing in here computes on the CPU -- if the CUDA
+ * device is missing every call fails with LOCUST_E_CUDA.
+ *
+ * Record contract (KeyIntValuePair, KeyValue.h:13-18, with the fixed widths
+ * lifted): the result is n records (key bytes, count) in ascending unsigned byte
+ * order ("strcmp order", a key that is a prefix of another sorts first), keys in
+ * one blob addressed by n+1 offsets, counts 64-bit.
+ *
+ * Input contract: bytes are split at the reference's delimiter literal
+ * " ,.-;:'()\"\t" (main.cu:138,:150) plus '\n' (getline, main.cu:43).  Everything
+ * else, including '\r' and bytes >= 0x80, is token content.  The input must not
+ * contain NUL bytes (the reference treats each line as a C string).
+ */
+#ifndef LOCUST_H
+#define LOCUST_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* status codes (the reference checks no status at all) */
+#define LOCUST_OK          0
+#define LOCUST_E_ARG       1   /* bad argument / NULL pointer                   */
+#define LOCUST_E_CUDA      2   /* a CUDA runtime call failed (text in last_error) */
+#define LOCUST_E_CAPACITY  3   /* a fixed-size buffer was too small even after growth */
+#define LOCUST_E_STATE     4   /* stage called out of order                      */
+#define LOCUST_E_NOMEM     5   /* host allocation failed                         */
+
+/* where the bytes handed to locust_map live */
+#define LOCUST_HOST    0
+#define LOCUST_DEVICE  1
+
+/* stages, for locust_stage_ms (the three chrono intervals of main.cu:405-418,:453-468) */
+#define LOCUST_STAGE_MAP      0
+#define LOCUST_STAGE_PROCESS  1
+#define LOCUST_STAGE_REDUCE   2
+
+/* config flags */
+#define LOCUST_F_GENERIC_TOKENISER  1u  /* test switch: byte-serial token path for every token */
+#define LOCUST_F_NO_SMEM_COMBINER   2u  /* test switch: every token goes to the global table     */
+#define LOCUST_F_WEAK_HASH          4u  /* test switch: 8-bit hashes, forces probe collisions    */
+
+typedef struct locust_ctx locust_ctx;
+
+typedef struct locust_config {
+    int32_t  device;         /* CUDA device ordinal                                             */
+    uint32_t table_log2;     /* global combiner table holds 1 << table_log2 slots of 32 B;
+                                0 = default (20).  It grows by itself when it fills.            */
+    uint32_t flags;          /* LOCUST_F_*                                                      */
+    uint32_t reserved;
+    uint64_t long_capacity;  /* occurrences of tokens longer than 16 bytes the job may hold
+                                before the buffer is grown; 0 = default (1 << 20)               */
+    void    *stream;         /* cudaStream_t to run on; NULL = a private non-blocking stream    */
+} locust_config;
+
+/* Replaces the allocations at the top of main() (main.cu:392-393, :402, :451):
+ * creates the per-device context that owns every device buffer of the path. */
+int locust_create(const locust_config *cfg, locust_ctx **out);
+
+/* Replaces the cudaFree/free tail of main() (main.cu:477-485). */
+int locust_destroy(locust_ctx *ctx);
+
+/* Forget the current job (counts, result) but keep the buffers: the equivalent of
+ * starting the reference binary again on another file. */
+int locust_reset(locust_ctx *ctx);
+
+/* MAP.  Replaces loadFile's record building + kernMap/map (main.cu:40-64,
+ * :136-159, launch :406) and the cudaMemcpy in front of it (:403): tokenises
+ * `nbytes` bytes and combines (word, 1) pairs into per-device (word, count)
+ * partials.  May be called several times before locust_process; every call must
+ * begin at a token boundary (start of input or right after a delimiter).
+ * LOCUST_DEVICE: `data` is a device pointer on ctx's device and must stay valid
+ * and unchanged until locust_reduce has returned (long keys are kept as pointers
+ * into it).  LOCUST_HOST: the bytes are copied to the device in chunks that
+ * overlap with tokenising; pinned host memory makes that copy asynchronous. */
+int locust_map(locust_ctx *ctx, const void *data, uint64_t nbytes, int where);
+
+/* PROCESS.  Replaces thrust::partition + thrust::sort with KIVComparator
+ * (main.cu:411-415; KeyValue.h:20-33, :79-84): compacts the combined records
+ * out of the table and sorts them by key bytes. */
+int locust_process(locust_ctx *ctx);
+
+/* REDUCE.  Replaces kernFindUniqBool -> thrust::partition -> kernGetCount
+ * (main.cu:161-238, host sequence :447-465): run-length merge over the sorted
+ * records, final counts, `val` (exclusive prefix sum of counts, the value the
+ * reference prints as "val", main.cu:132) and the key blob. */
+int locust_reduce(locust_ctx *ctx);
+
+/* map + process + reduce in one call (single mode, main.cu:397-468). */
+int locust_wordcount(locust_ctx *ctx, const void *data, uint64_t nbytes, int where);
+
+/* Replaces the cudaMemcpy device->host of the result (main.cu:470-472).  Pointers
+ * are borrowed: valid until the next locust_reset / locust_map / locust_destroy.
+ * offsets has n + 1 entries; vals may be NULL. */
+int locust_result_host(locust_ctx *ctx, const uint8_t **key_blob, const uint64_t **key_offsets,
+                       const uint64_t **counts, const uint64_t **vals, uint64_t *n);
+
+/* Same records, left in device memory (for callers that keep going on the GPU). */
+int locust_result_device(locust_ctx *ctx, const uint8_t **key_blob, const uint64_t **key_offsets,
+                         const uint64_t **counts, const uint64_t **vals, uint64_t *n);
+
+/* printKeyIntValues (main.cu:126-134, line format :132)
+ *   "print key: %s \t val: %d \t count: %d\n"
+ * or, with cpu_format != 0, printKeyValues of the CPU branch (main.cu:286)
+ *   "print key: %s \t value: %s\n".
+ * Lines are formatted on the device and copied out in one piece.  Returns the
+ * text through *text (borrowed, host memory, not NUL-terminated) and *nbytes. */
+int locust_format_result(locust_ctx *ctx, int cpu_format, const char **text, uint64_t *nbytes);
+
+/* Device time of a stage in milliseconds (CUDA events on the context's stream):
+ * what main.cu:408,:418,:468 print, but measured on the device. */
+float locust_stage_ms(locust_ctx *ctx, int stage);
+
+/* Number of tokens counted (sum of all counts) and of kernels launched by the job
+ * so far. */
+int locust_stats(locust_ctx *ctx, uint64_t *tokens, uint64_t *unique_keys, uint64_t *kernel_launches);
+
+/* Text of the last error on this context ("" if none). */
+const char *locust_last_error(locust_ctx *ctx);
+
+/* ---- multi-GPU shuffle: replaces writeKeyIntValues -> /tmp/out.txt ->
+ * loadIntermediateFile (main.cu:116-124, :428-430, :66-103, :441) -------------- */
+
+/* After locust_map: splits this device's partial (word, count) records by
+ * hash(word) % nparts and reports how many bytes each part packs to.
+ * bytes_per_part: host array of nparts. */
+int locust_shuffle_sizes(locust_ctx *ctx, uint32_t nparts, uint64_t *bytes_per_part);
+
+/* Packs part p at dev_out + part_offsets[p] (device memory, caller-owned; offsets
+ * and sizes as reported by locust_shuffle_sizes, each a multiple of 32). */
+int locust_shuffle_pack(locust_ctx *ctx, uint32_t nparts, void *dev_out, const uint64_t *part_offsets);
+
+/* Drops the local partials (they have been packed) and starts the final table. */
+int locust_shuffle_begin_merge(locust_ctx *ctx);
+
+/* Adds packed records received from a peer (device memory; must stay valid until
+ * locust_reduce has returned). */
+int locust_shuffle_merge(locust_ctx *ctx, const void *dev_records, uint64_t nbytes);
+
+/* Library version string. */
+const char *locust_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LOCUST_H */

@@ -1,0 +1,230 @@
+"""locust_b200 -- host-side mirror of Locust's MapReduce word-count operator surface.
+
+The product is liblocust.so (hand-written sm_100a CUDA behind the C ABI of
+include/locust.h); this module only binds it with ctypes and keeps the reference's
+vocabulary: a job runs map -> process -> reduce (MapReduce/src/main.cu:397-468) and
+yields (key, count) records in strcmp order.
+
+There is no CPU path here: if the library or a CUDA device is missing every call
+raises LocustError.
+"""
+import ctypes
+import os
+
+__all__ = ["LocustError", "WordCount", "lib_path", "load", "HOST", "DEVICE",
+           "F_GENERIC_TOKENISER", "F_NO_SMEM_COMBINER", "F_WEAK_HASH"]
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+HOST, DEVICE = 0, 1
+STAGE_MAP, STAGE_PROCESS, STAGE_REDUCE = 0, 1, 2
+F_GENERIC_TOKENISER, F_NO_SMEM_COMBINER, F_WEAK_HASH = 1, 2, 4
+
+EXPORTS = [
+    "locust_version", "locust_create", "locust_destroy", "locust_reset", "locust_map",
+    "locust_process", "locust_reduce", "locust_wordcount", "locust_result_host",
+    "locust_result_device", "locust_format_result", "locust_stage_ms", "locust_stats",
+    "locust_last_error", "locust_shuffle_sizes", "locust_shuffle_pack",
+    "locust_shuffle_begin_merge", "locust_shuffle_merge",
+]
+
+
+class LocustError(RuntimeError):
+    pass
+
+
+class _Config(ctypes.Structure):
+    _fields_ = [("device", ctypes.c_int32), ("table_log2", ctypes.c_uint32), ("flags", ctypes.c_uint32),
+                ("reserved", ctypes.c_uint32), ("long_capacity", ctypes.c_uint64), ("stream", ctypes.c_void_p)]
+
+
+def lib_path():
+    return os.path.join(_HERE, "liblocust.so")
+
+
+_lib = None
+
+
+def load():
+    """Loads liblocust.so (built in-tree by __graft_entry__.build()).  Fails loudly."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    p = lib_path()
+    if not os.path.exists(p):
+        raise LocustError("liblocust.so is not built: run `python -c 'import __graft_entry__ as g; g.build()'`")
+    L = ctypes.CDLL(p)
+    vp, u64, u32 = ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32
+    pp = ctypes.POINTER
+    L.locust_version.restype = ctypes.c_char_p
+    L.locust_create.argtypes = [pp(_Config), pp(vp)]
+    L.locust_destroy.argtypes = [vp]
+    L.locust_reset.argtypes = [vp]
+    L.locust_map.argtypes = [vp, vp, u64, ctypes.c_int]
+    L.locust_process.argtypes = [vp]
+    L.locust_reduce.argtypes = [vp]
+    L.locust_wordcount.argtypes = [vp, vp, u64, ctypes.c_int]
+    L.locust_result_host.argtypes = [vp, pp(vp), pp(vp), pp(vp), pp(vp), pp(u64)]
+    L.locust_result_device.argtypes = [vp, pp(vp), pp(vp), pp(vp), pp(vp), pp(u64)]
+    L.locust_format_result.argtypes = [vp, ctypes.c_int, pp(vp), pp(u64)]
+    L.locust_stage_ms.argtypes = [vp, ctypes.c_int]
+    L.locust_stage_ms.restype = ctypes.c_float
+    L.locust_stats.argtypes = [vp, pp(u64), pp(u64), pp(u64)]
+    L.locust_last_error.argtypes = [vp]
+    L.locust_last_error.restype = ctypes.c_char_p
+    L.locust_shuffle_sizes.argtypes = [vp, u32, pp(u64)]
+    L.locust_shuffle_pack.argtypes = [vp, u32, vp, pp(u64)]
+    L.locust_shuffle_begin_merge.argtypes = [vp]
+    L.locust_shuffle_merge.argtypes = [vp, vp, u64]
+    _lib = L
+    return L
+
+
+def _ptr_of(data):
+    """(address, nbytes, where, keepalive) for bytes-like, numpy arrays and torch tensors."""
+    if hasattr(data, "data_ptr"):                       # torch tensor (uint8, contiguous)
+        if not data.is_contiguous():
+            raise LocustError("input tensor must be contiguous")
+        n = data.numel() * data.element_size()
+        return data.data_ptr(), n, (DEVICE if data.is_cuda else HOST), data
+    if hasattr(data, "ctypes") and hasattr(data, "nbytes"):   # numpy
+        return data.ctypes.data, data.nbytes, HOST, data
+    b = bytes(data)
+    return ctypes.cast(ctypes.c_char_p(b), ctypes.c_void_p).value or 0, len(b), HOST, b
+
+
+class WordCount:
+    """One word-count job context on one GPU: the three stages of the reference's
+    main() as methods, results as (keys, counts)."""
+
+    def __init__(self, device=0, table_log2=0, flags=0, long_capacity=0, stream=None):
+        L = load()
+        cfg = _Config(device, table_log2, flags, 0, long_capacity, stream)
+        h = ctypes.c_void_p()
+        rc = L.locust_create(ctypes.byref(cfg), ctypes.byref(h))
+        self._L, self._h = L, h
+        self._keep = []
+        if rc != 0:
+            msg = L.locust_last_error(h).decode() if h else "no usable CUDA device"
+            if h:
+                L.locust_destroy(h)
+            self._h = None
+            raise LocustError("locust_create failed (%d): %s" % (rc, msg))
+
+    # -- plumbing -------------------------------------------------------------
+    def _check(self, rc, what):
+        if rc != 0:
+            raise LocustError("%s failed (%d): %s" % (what, rc, self._L.locust_last_error(self._h).decode()))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.locust_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # -- stages (main.cu:406, :411-415, :447-465) -------------------------------
+    def reset(self):
+        self._check(self._L.locust_reset(self._h), "locust_reset")
+        self._keep = []
+
+    def map(self, data):
+        ptr, n, where, keep = _ptr_of(data)
+        self._keep.append(keep)            # device inputs must outlive reduce()
+        self._check(self._L.locust_map(self._h, ptr, n, where), "locust_map")
+
+    def process(self):
+        self._check(self._L.locust_process(self._h), "locust_process")
+
+    def reduce(self):
+        self._check(self._L.locust_reduce(self._h), "locust_reduce")
+
+    def run(self, data):
+        """reset + map + process + reduce."""
+        self.reset()
+        self.map(data)
+        self.process()
+        self.reduce()
+        return self
+
+    # -- results ------------------------------------------------------------------
+    def result(self):
+        """(keys: list[bytes] in strcmp order, counts: list[int], vals: list[int])."""
+        vp, u64 = ctypes.c_void_p, ctypes.c_uint64
+        blob, offs, cnts, vals, n = vp(), vp(), vp(), vp(), u64()
+        self._check(self._L.locust_result_host(self._h, ctypes.byref(blob), ctypes.byref(offs), ctypes.byref(cnts),
+                                               ctypes.byref(vals), ctypes.byref(n)), "locust_result_host")
+        n = n.value
+        o = (u64 * (n + 1)).from_address(offs.value)
+        offsets = list(o)
+        b = ctypes.string_at(blob.value, offsets[n]) if n else b""
+        keys = [b[offsets[i]:offsets[i + 1]] for i in range(n)]
+        counts = list((u64 * n).from_address(cnts.value)) if n else []
+        values = list((u64 * n).from_address(vals.value)) if n else []
+        return keys, counts, values
+
+    def result_arrays(self):
+        """numpy views (copied) of blob, offsets, counts, vals -- for large results."""
+        import numpy as np
+        vp, u64 = ctypes.c_void_p, ctypes.c_uint64
+        blob, offs, cnts, vals, n = vp(), vp(), vp(), vp(), u64()
+        self._check(self._L.locust_result_host(self._h, ctypes.byref(blob), ctypes.byref(offs), ctypes.byref(cnts),
+                                               ctypes.byref(vals), ctypes.byref(n)), "locust_result_host")
+        n = n.value
+        offsets = np.ctypeslib.as_array((u64 * (n + 1)).from_address(offs.value)).copy()
+        nb = int(offsets[n])
+        b = np.ctypeslib.as_array((ctypes.c_uint8 * max(nb, 1)).from_address(blob.value))[:nb].copy()
+        c = np.ctypeslib.as_array((u64 * max(n, 1)).from_address(cnts.value))[:n].copy()
+        v = np.ctypeslib.as_array((u64 * max(n, 1)).from_address(vals.value))[:n].copy()
+        return b, offsets, c, v
+
+    def device_result(self):
+        """(blob_ptr, offsets_ptr, counts_ptr, vals_ptr, n) -- raw device addresses."""
+        vp, u64 = ctypes.c_void_p, ctypes.c_uint64
+        blob, offs, cnts, vals, n = vp(), vp(), vp(), vp(), u64()
+        self._check(self._L.locust_result_device(self._h, ctypes.byref(blob), ctypes.byref(offs), ctypes.byref(cnts),
+                                                 ctypes.byref(vals), ctypes.byref(n)), "locust_result_device")
+        return blob.value, offs.value, cnts.value, vals.value, n.value
+
+    def format(self, cpu_format=False):
+        """The reference's `print key:` lines (main.cu:132, or :286 with cpu_format)."""
+        t, nb = ctypes.c_void_p(), ctypes.c_uint64()
+        self._check(self._L.locust_format_result(self._h, 1 if cpu_format else 0, ctypes.byref(t), ctypes.byref(nb)),
+                    "locust_format_result")
+        return ctypes.string_at(t.value, nb.value) if nb.value else b""
+
+    def stage_ms(self):
+        return tuple(float(self._L.locust_stage_ms(self._h, s)) for s in (0, 1, 2))
+
+    def stats(self):
+        u64 = ctypes.c_uint64
+        t, u, k = u64(), u64(), u64()
+        self._check(self._L.locust_stats(self._h, ctypes.byref(t), ctypes.byref(u), ctypes.byref(k)), "locust_stats")
+        return {"tokens": t.value, "unique_keys": u.value, "kernel_launches": k.value}
+
+    # -- multi-GPU shuffle ---------------------------------------------------------
+    def shuffle_sizes(self, nparts):
+        arr = (ctypes.c_uint64 * nparts)()
+        self._check(self._L.locust_shuffle_sizes(self._h, nparts, arr), "locust_shuffle_sizes")
+        return list(arr)
+
+    def shuffle_pack(self, nparts, dev_out_ptr, part_offsets):
+        arr = (ctypes.c_uint64 * nparts)(*part_offsets)
+        self._check(self._L.locust_shuffle_pack(self._h, nparts, dev_out_ptr, arr), "locust_shuffle_pack")
+
+    def shuffle_begin_merge(self):
+        self._check(self._L.locust_shuffle_begin_merge(self._h), "locust_shuffle_begin_merge")
+
+    def shuffle_merge(self, dev_ptr, nbytes, keepalive=None):
+        if keepalive is not None:
+            self._keep.append(keepalive)
+        self._check(self._L.locust_shuffle_merge(self._h, dev_ptr, nbytes), "locust_shuffle_merge")

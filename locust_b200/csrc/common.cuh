@@ -1,0 +1,131 @@
+// common.cuh -- shared device/host helpers of the word-count path (sm_100a).
+//
+// Byte classification follows the reference's delimiter literal
+// " ,.-;:'()\"\t" (MapReduce/src/main.cu:138,:150) plus '\n' (getline, main.cu:43);
+// key order follows KIVComparator (KeyValue.h:20-33): unsigned bytes, first
+// difference decides, shorter prefix first.
+#pragma once
+#include <stdint.h>
+#include <cuda_runtime.h>
+
+#if defined(__CUDACC__)
+#define LC_HD __host__ __device__ __forceinline__
+#define LC_D __device__ __forceinline__
+#else
+#define LC_HD inline
+#define LC_D inline
+#endif
+
+namespace locust {
+
+// One bit per byte value < 64: '\t' '\n' ' ' '"' '\'' '(' ')' ',' '-' '.' ':' ';'
+constexpr uint64_t kDelimMask64 = 0x0C00738500000600ull;
+
+LC_HD bool is_delim(uint32_t c) { return c < 64u && ((kDelimMask64 >> c) & 1ull); }
+
+// SWAR classifier: for the four bytes of x, returns 0x80 in every byte that is a
+// delimiter, 0 elsewhere.  Thresholds t are applied to the low seven bits
+// (x7 + (0x80 - t) sets the top bit iff x7 >= t); the delimiter set is a union of
+// the ranges [09,0A] [27,29] [2C,2E] [3A,3B], whose membership is the parity of
+// the thresholds passed, plus {20,22}, tested as ((x7 & 7D) ^ 20) == 0.  Bytes
+// with the top bit set are never delimiters.
+LC_HD uint32_t classify4(uint32_t x) {
+    const uint32_t x7 = x & 0x7F7F7F7Fu;
+    const uint32_t r1 = x7 + 0x77777777u;   // >= 09
+    const uint32_t r2 = x7 + 0x75757575u;   // >= 0B
+    const uint32_t r3 = x7 + 0x59595959u;   // >= 27
+    const uint32_t r4 = x7 + 0x56565656u;   // >= 2A
+    const uint32_t r5 = x7 + 0x54545454u;   // >= 2C
+    const uint32_t r6 = x7 + 0x51515151u;   // >= 2F
+    const uint32_t r7 = x7 + 0x46464646u;   // >= 3A
+    const uint32_t r8 = x7 + 0x44444444u;   // >= 3C
+    const uint32_t z  = (x7 & 0x7D7D7D7Du) ^ 0x20202020u;
+    const uint32_t nz = z + 0x7F7F7F7Fu;    // top bit iff z != 0
+    const uint32_t a = r1 ^ r2 ^ r3;
+    const uint32_t b = r4 ^ r5 ^ r6;
+    const uint32_t c = r7 ^ r8 ^ ~nz;
+    return (a ^ b ^ c) & ~x & 0x80808080u;
+}
+
+// Gathers the four 0x80 flags of classify4 into bits 0..3.
+LC_HD uint32_t gather4(uint32_t flags) { return (flags * 0x00204081u) >> 28; }
+
+// 16-bit delimiter mask of a 16-byte chunk (bit i = byte i is a delimiter).
+LC_HD uint32_t classify16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
+    const uint32_t p0 = classify4(w0) * 0x00204081u;
+    const uint32_t p1 = classify4(w1) * 0x00204081u;
+    const uint32_t p2 = classify4(w2) * 0x00204081u;
+    const uint32_t p3 = classify4(w3) * 0x00204081u;
+    return (p0 >> 28) | ((p1 >> 24) & 0xF0u) | ((p2 >> 20) & 0xF00u) | ((p3 >> 16) & 0xF000u);
+}
+
+LC_HD uint32_t byte_perm(uint32_t a, uint32_t b, uint32_t s) {
+#if defined(__CUDA_ARCH__)
+    return __byte_perm(a, b, s);
+#else
+    // PTX prmt, default mode: nibble i of s picks one of the 8 bytes {a,b}; bit 3
+    // of the nibble replicates that byte's sign bit instead.
+    uint64_t t = ((uint64_t)b << 32) | a;
+    uint32_t r = 0;
+    for (int i = 0; i < 4; i++) {
+        uint32_t n = (s >> (4 * i)) & 0xF;
+        uint32_t v = (uint32_t)(t >> (8 * (n & 7))) & 0xFF;
+        if (n & 8) v = (v & 0x80) ? 0xFF : 0x00;
+        r |= v << (8 * i);
+    }
+    return r;
+#endif
+}
+
+// Key of a token of L <= 8 ASCII bytes starting at byte `o` (0..3) of word wa,
+// with wb, wc the following words: the token's bytes, zero padded, as a
+// little-endian 64-bit value (lo = bytes 0..3, hi = bytes 4..7).  Bytes past L
+// are zeroed by setting bit 3 of their selector nibble, which yields 0x00 for any
+// byte below 0x80 -- callers only use this on all-ASCII chunks.
+LC_HD void extract_key8(uint32_t wa, uint32_t wb, uint32_t wc, uint32_t o, uint32_t L,
+                        uint32_t &lo, uint32_t &hi) {
+    const uint32_t sel = 0x3210u + 0x1111u * o;
+    const uint32_t z = (L >= 8u) ? 0u : (0x88888888u << (4u * L));
+    lo = byte_perm(wa, wb, sel | (z & 0xFFFFu));
+    hi = byte_perm(wb, wc, sel | (z >> 16));
+}
+
+// Index of the lowest set bit of a 4-bit value (0 for 0), from a 32-bit table.
+LC_HD uint32_t low_bit4(uint32_t n) { return (0x12131210u >> (2u * n)) & 3u; }
+
+LC_HD uint64_t bswap64(uint64_t v) {
+    v = ((v & 0x00FF00FF00FF00FFull) << 8) | ((v >> 8) & 0x00FF00FF00FF00FFull);
+    v = ((v & 0x0000FFFF0000FFFFull) << 16) | ((v >> 16) & 0x0000FFFF0000FFFFull);
+    return (v << 32) | (v >> 32);
+}
+
+// 64-bit mix (splitmix64 finaliser) -- table slot hash for (k0, k1) keys.
+LC_HD uint64_t mix64(uint64_t x) {
+    x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull;
+    x ^= x >> 27; x *= 0x94d049bb133111ebull;
+    x ^= x >> 31;
+    return x;
+}
+LC_HD uint64_t hash_key128(uint64_t k0, uint64_t k1) {
+    return mix64(k0 ^ (k1 * 0x9E3779B97F4A7C15ull) ^ (k1 >> 29));
+}
+
+// ---- global combiner table -------------------------------------------------
+// One slot = 32 bytes: key (k0, k1) = the token's bytes zero padded to 16,
+// little endian (k0 = bytes 0..7).  Tokens contain no NUL, so the padded value
+// identifies the token exactly and an all-zero key marks an empty slot.
+struct __align__(32) Slot {
+    uint64_t k0, k1;
+    unsigned long long count;
+    uint64_t pad;
+};
+
+// A sorted/unsorted record of the process stage: be0/be1 = first 16 key bytes,
+// big endian and zero padded (so integer order = byte order, prefix first);
+// for keys longer than 16 bytes `ptr` addresses the full key and len > 16.
+struct __align__(16) LongRef {
+    const uint8_t *ptr;
+    uint64_t len;
+};
+
+}  // namespace locust

@@ -1,0 +1,117 @@
+// kernels.cuh -- launch interfaces between the C ABI (locust_api.cu) and the
+// hand-written sm_100a kernels of the word-count path.
+//
+// Every kernel after MAP reads its problem size from device memory (Counters), so
+// the three stages run back to back on one stream without a host round trip; the
+// host reads Counters once, at the end of REDUCE.
+#pragma once
+#include "common.cuh"
+
+namespace locust {
+
+// status bits written by kernels
+constexpr uint32_t kStatusTableFull = 1u;   // global combiner table ran out of probes
+constexpr uint32_t kStatusLongFull  = 2u;   // long-token buffer too small
+constexpr uint32_t kStatusEntryFull = 4u;   // candidate-record buffers too small
+constexpr uint32_t kStatusBlobFull  = 8u;   // key blob too small
+constexpr uint32_t kStatusTextFull  = 16u;  // formatted-text buffer too small
+
+// One occurrence of a token longer than 16 bytes / the full key of a record.
+struct LongTok {
+    const uint8_t *ptr;   // nullptr for keys of <= 16 bytes
+    uint64_t len;
+};
+
+// Device-side scalars of one job.
+struct Counters {
+    unsigned long long n_long;      // long-token occurrences seen (can exceed the buffer)
+    unsigned long long n_entries;   // candidate records after extract + append
+    unsigned long long n_out;       // unique keys
+    unsigned long long blob_bytes;  // sum of key lengths
+    unsigned long long total;       // sum of counts = tokens
+    unsigned long long text_bytes;  // formatted output size
+    uint32_t status;
+    uint32_t sort_parity;           // 0: sorted records in buffer A, 1: in buffer B
+    uint32_t pass_active[16];       // radix pass p moves data
+    uint32_t pass_src[16];          // buffer pass p reads (0 = A, 1 = B)
+};
+
+struct MapParams {
+    const uint8_t *base;        // 16-byte aligned; valid bytes are base[lo .. hi)
+    uint64_t lo, hi;
+    Slot *table;
+    uint64_t table_mask;        // slots - 1
+    LongTok *long_list;
+    uint64_t long_cap;
+    Counters *ctr;
+    uint32_t flags;             // LOCUST_F_*
+};
+
+// Candidate records.  Sort buffers A/B hold (be0, be1, idx): the first 16 key
+// bytes big endian and zero padded (integer order = byte order, prefix first) and
+// the index of the record's payload (count, ref).
+struct Records {
+    uint64_t *a0, *a1, *b0, *b1;
+    uint32_t *ia, *ib;
+    unsigned long long *count;   // by payload index
+    LongTok *ref;                // by payload index
+    uint64_t cap;
+};
+
+struct SortScratch {
+    uint32_t *hist;          // 16 * 256 digit histograms
+    uint32_t *bases;         // 16 * 256 exclusive bases
+    uint64_t *lb_state;      // look-back words: tiles * 256
+    uint32_t *tickets;       // pairs of {next tile, finished blocks}
+};
+
+struct ReduceBufs {
+    uint8_t *head;                   // cap flags
+    unsigned long long *rank;        // cap
+    uint32_t *src_pos;               // cap: sorted position of each output key
+    uint64_t *key_offsets;           // cap + 1
+    unsigned long long *counts;      // cap
+    unsigned long long *vals;        // cap
+    uint8_t *key_blob;
+    uint64_t blob_cap;
+};
+
+constexpr uint32_t kSortTile = 2048;
+constexpr uint32_t kScanTile = 2048;
+
+cudaError_t map_kernel_setup();
+int launch_tokenize_combine(const MapParams &p, int num_sms, cudaStream_t st);
+
+// PROCESS
+int launch_extract(const Slot *table, uint64_t slots, Records r, Counters *ctr, int num_sms, cudaStream_t st);
+int launch_append_long(const LongTok *list, uint64_t long_cap, Records r, Counters *ctr, int num_sms, cudaStream_t st);
+// epoch: first of 16 consecutive look-back epochs this sort may use
+int launch_sort_records(Records r, SortScratch s, Counters *ctr, uint32_t epoch, int num_sms, cudaStream_t st);
+int launch_tie_fix(Records r, Counters *ctr, int num_sms, cudaStream_t st);
+
+// REDUCE.  epoch: first of 3 consecutive epochs.
+int launch_reduce(Records r, SortScratch s, ReduceBufs o, Counters *ctr, uint32_t epoch, int num_sms, cudaStream_t st);
+
+// OUTPUT: "print key: ..." lines (main.cu:132 / :286).  Two steps so the host can
+// size the text buffer in between.
+int launch_format_sizes(ReduceBufs o, Counters *ctr, int cpu_format, unsigned long long *line_off,
+                        SortScratch s, uint32_t epoch, int num_sms, cudaStream_t st);
+int launch_format_write(ReduceBufs o, Counters *ctr, int cpu_format, const unsigned long long *line_off,
+                        char *text, uint64_t text_cap, int num_sms, cudaStream_t st);
+
+// Device-wide exclusive scan of 64-bit values; n is read from *n_ptr.  `out` may
+// equal `in`.  The grand total goes to *total (if non-null) and, when
+// append_total is set, to out[n].
+int launch_exclusive_scan_u64(const unsigned long long *in, unsigned long long *out, const unsigned long long *n_ptr,
+                              uint64_t n_max, uint64_t *lb_state, uint32_t *ticket, uint32_t epoch,
+                              unsigned long long *total, bool append_total, int num_sms, cudaStream_t st);
+
+// SHUFFLE (multi-GPU): records of 32 bytes {k0, k1, count, 0}
+int launch_shuffle_count(const Slot *table, uint64_t slots, uint32_t nparts, unsigned long long *part_counts,
+                         int num_sms, cudaStream_t st);
+int launch_shuffle_pack(const Slot *table, uint64_t slots, uint32_t nparts, uint8_t *out,
+                        const unsigned long long *part_offsets, unsigned long long *part_cursors, int num_sms,
+                        cudaStream_t st);
+int launch_shuffle_merge(const uint8_t *records, uint64_t nrec, MapParams p, int num_sms, cudaStream_t st);
+
+}  // namespace locust

@@ -1,0 +1,538 @@
+// locust_api.cu -- the C ABI of liblocust.so (include/locust.h): per-device context,
+// stage sequencing, buffer ownership, growth and the host copies of the result.
+// Plays the role of main() in MapReduce/src/main.cu:358-532 minus argv and stdout.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+#include "../../include/locust.h"
+
+using namespace locust;
+
+namespace {
+
+struct Segment {
+    const uint8_t *dev;   // device bytes
+    uint64_t nbytes;
+    uint8_t *owned;       // non-null when the context made the device copy
+};
+
+constexpr uint64_t kHostChunk = 32ull << 20;   // host->device copy granularity
+
+}  // namespace
+
+struct locust_ctx {
+    int device = 0;
+    int num_sms = 0;
+    cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;
+    bool own_stream = false;
+    uint32_t flags = 0;
+
+    Slot *table = nullptr;
+    uint64_t slots = 0;
+    LongTok *long_list = nullptr;
+    uint64_t long_cap = 0;
+    Counters *ctr = nullptr;        // device
+    Counters *h_ctr = nullptr;      // pinned host mirror
+    Records rec{};
+    SortScratch sort{};
+    ReduceBufs red{};
+    uint64_t lb_words = 0;
+    uint32_t epoch = 1;
+
+    std::vector<Segment> segments;
+    bool cleared = false;           // table/counters zeroed for the current job
+    bool shuffled = false;          // partials were packed; the table now holds merged records
+    int stage = 0;                  // 0 mapping, 1 processed, 2 reduced
+
+    // host copies of the result (pinned)
+    uint8_t *h_blob = nullptr;  uint64_t h_blob_cap = 0;
+    uint64_t *h_offsets = nullptr, *h_counts = nullptr, *h_vals = nullptr;  uint64_t h_rec_cap = 0;
+    bool host_valid = false;
+    // formatted text
+    unsigned long long *line_off = nullptr;  uint64_t line_cap = 0;
+    char *d_text = nullptr;  uint64_t d_text_cap = 0;
+    char *h_text = nullptr;  uint64_t h_text_cap = 0;
+    // shuffle scratch
+    unsigned long long *part_counts = nullptr;  uint32_t part_cap = 0;
+
+    cudaEvent_t ev[6]{};            // map, process, reduce: begin/end
+    bool ev_set[6]{};
+    uint64_t launches = 0;
+    std::string err;
+};
+
+namespace {
+
+int fail(locust_ctx *c, int code, const char *what, cudaError_t e = cudaSuccess) {
+    if (c) {
+        c->err = what;
+        if (e != cudaSuccess) { c->err += ": "; c->err += cudaGetErrorString(e); }
+    }
+    return code;
+}
+
+#define CU(call)                                                              \
+    do {                                                                      \
+        cudaError_t e_ = (call);                                              \
+        if (e_ != cudaSuccess) return fail(c, LOCUST_E_CUDA, #call, e_);      \
+    } while (0)
+
+template <class T>
+cudaError_t dalloc(T **p, uint64_t n) { return cudaMalloc(reinterpret_cast<void **>(p), n * sizeof(T)); }
+
+void free_record_buffers(locust_ctx *c) {
+    cudaFree(c->rec.a0); cudaFree(c->rec.a1); cudaFree(c->rec.b0); cudaFree(c->rec.b1);
+    cudaFree(c->rec.ia); cudaFree(c->rec.ib); cudaFree(c->rec.count); cudaFree(c->rec.ref);
+    cudaFree(c->sort.lb_state);
+    cudaFree(c->red.head); cudaFree(c->red.rank); cudaFree(c->red.src_pos); cudaFree(c->red.key_offsets);
+    cudaFree(c->red.counts); cudaFree(c->red.vals); cudaFree(c->red.key_blob);
+    c->rec = Records{};
+    c->red = ReduceBufs{};
+    c->sort.lb_state = nullptr;
+}
+
+// (re)allocates everything whose size follows the table and long-token capacities
+int alloc_sized(locust_ctx *c, uint64_t slots, uint64_t long_cap) {
+    cudaFree(c->table); c->table = nullptr;
+    cudaFree(c->long_list); c->long_list = nullptr;
+    free_record_buffers(c);
+    c->slots = slots;
+    c->long_cap = long_cap;
+    const uint64_t cap = slots + long_cap;
+    CU(dalloc(&c->table, slots));
+    CU(dalloc(&c->long_list, long_cap));
+    CU(dalloc(&c->rec.a0, cap)); CU(dalloc(&c->rec.a1, cap));
+    CU(dalloc(&c->rec.b0, cap)); CU(dalloc(&c->rec.b1, cap));
+    CU(dalloc(&c->rec.ia, cap)); CU(dalloc(&c->rec.ib, cap));
+    CU(dalloc(&c->rec.count, cap)); CU(dalloc(&c->rec.ref, cap));
+    c->rec.cap = cap;
+    c->lb_words = ((cap + kSortTile - 1) / kSortTile) * 256 + 256;
+    CU(dalloc(&c->sort.lb_state, c->lb_words));
+    CU(cudaMemsetAsync(c->sort.lb_state, 0, c->lb_words * sizeof(uint64_t), c->stream));
+    c->epoch = 1;
+    CU(dalloc(&c->red.head, cap)); CU(dalloc(&c->red.rank, cap)); CU(dalloc(&c->red.src_pos, cap));
+    CU(dalloc(&c->red.key_offsets, cap + 1)); CU(dalloc(&c->red.counts, cap)); CU(dalloc(&c->red.vals, cap));
+    c->red.blob_cap = 16 * slots + 64 * long_cap;
+    CU(dalloc(&c->red.key_blob, c->red.blob_cap));
+    return LOCUST_OK;
+}
+
+uint32_t take_epochs(locust_ctx *c, uint32_t k) {
+    if (c->epoch + k > 255u) {
+        cudaMemsetAsync(c->sort.lb_state, 0, c->lb_words * sizeof(uint64_t), c->stream);
+        c->epoch = 1;
+    }
+    const uint32_t e = c->epoch;
+    c->epoch += k;
+    return e;
+}
+
+int clear_job(locust_ctx *c) {
+    CU(cudaMemsetAsync(c->table, 0, c->slots * sizeof(Slot), c->stream));
+    CU(cudaMemsetAsync(c->ctr, 0, sizeof(Counters), c->stream));
+    c->cleared = true;
+    c->shuffled = false;
+    c->stage = 0;
+    c->host_valid = false;
+    return LOCUST_OK;
+}
+
+void drop_segments(locust_ctx *c) {
+    for (auto &s : c->segments) cudaFree(s.owned);
+    c->segments.clear();
+}
+
+MapParams map_params(locust_ctx *c, const uint8_t *dev, uint64_t lo_abs, uint64_t hi_abs) {
+    // dev + lo_abs .. dev + hi_abs, expressed against a 16-byte aligned base
+    MapParams p{};
+    const uintptr_t a = reinterpret_cast<uintptr_t>(dev);
+    const uintptr_t base = a & ~uintptr_t(15);
+    p.base = reinterpret_cast<const uint8_t *>(base);
+    p.lo = (a - base) + lo_abs;
+    p.hi = (a - base) + hi_abs;
+    p.table = c->table;
+    p.table_mask = c->slots - 1;
+    p.long_list = c->long_list;
+    p.long_cap = c->long_cap;
+    p.ctr = c->ctr;
+    p.flags = c->flags;
+    return p;
+}
+
+int map_device_range(locust_ctx *c, const uint8_t *dev, uint64_t lo, uint64_t hi) {
+    if (hi <= lo) return LOCUST_OK;
+    c->launches += (uint64_t)launch_tokenize_combine(map_params(c, dev, lo, hi), c->num_sms, c->stream);
+    CU(cudaGetLastError());
+    return LOCUST_OK;
+}
+
+bool host_is_delim(uint8_t ch) { return is_delim(ch); }
+
+// HOST input: copy in chunks that end right after a delimiter and tokenise chunk k
+// while chunk k+1 is on the wire.
+int map_host(locust_ctx *c, const uint8_t *host, uint64_t nbytes, uint8_t *dev) {
+    uint64_t done = 0;
+    cudaEvent_t ev;
+    CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    // the copy stream must not overtake work already queued on the compute stream
+    CU(cudaEventRecord(ev, c->stream));
+    CU(cudaStreamWaitEvent(c->copy_stream, ev, 0));
+    int rc = LOCUST_OK;
+    while (done < nbytes) {
+        uint64_t end = done + kHostChunk;
+        if (end >= nbytes) end = nbytes;
+        else {
+            // cut after the last delimiter of the chunk so no token straddles two launches
+            uint64_t e = end;
+            while (e > done && !host_is_delim(host[e - 1])) --e;
+            if (e > done) end = e;
+            else {                               // one token longer than the chunk: extend to its end
+                while (end < nbytes && !host_is_delim(host[end])) ++end;
+            }
+        }
+        cudaError_t e1 = cudaMemcpyAsync(dev + done, host + done, end - done, cudaMemcpyHostToDevice, c->copy_stream);
+        if (e1 != cudaSuccess) { rc = fail(c, LOCUST_E_CUDA, "cudaMemcpyAsync(H2D)", e1); break; }
+        cudaEventRecord(ev, c->copy_stream);
+        cudaStreamWaitEvent(c->stream, ev, 0);
+        rc = map_device_range(c, dev, done, end);
+        if (rc) break;
+        done = end;
+    }
+    cudaEventDestroy(ev);
+    return rc;
+}
+
+int run_map_segment(locust_ctx *c, const Segment &s) { return map_device_range(c, s.dev, 0, s.nbytes); }
+
+int run_process(locust_ctx *c) {
+    CU(cudaEventRecord(c->ev[2], c->stream)); c->ev_set[2] = true;
+    c->launches += (uint64_t)launch_extract(c->table, c->slots, c->rec, c->ctr, c->num_sms, c->stream);
+    c->launches += (uint64_t)launch_append_long(c->long_list, c->long_cap, c->rec, c->ctr, c->num_sms, c->stream);
+    c->launches += (uint64_t)launch_sort_records(c->rec, c->sort, c->ctr, take_epochs(c, 16), c->num_sms, c->stream);
+    c->launches += (uint64_t)launch_tie_fix(c->rec, c->ctr, c->num_sms, c->stream);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(c->ev[3], c->stream)); c->ev_set[3] = true;
+    c->stage = 1;
+    return LOCUST_OK;
+}
+
+int run_reduce_async(locust_ctx *c) {
+    CU(cudaEventRecord(c->ev[4], c->stream)); c->ev_set[4] = true;
+    c->launches += (uint64_t)launch_reduce(c->rec, c->sort, c->red, c->ctr, take_epochs(c, 3), c->num_sms, c->stream);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(c->ev[5], c->stream)); c->ev_set[5] = true;
+    CU(cudaMemcpyAsync(c->h_ctr, c->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+    return LOCUST_OK;
+}
+
+// Runs REDUCE, reads the counters back and, if a fixed-size buffer was too small,
+// grows it and redoes the job from the recorded input segments.
+int finish_reduce(locust_ctx *c) {
+    for (int attempt = 0; attempt < 8; ++attempt) {
+        int rc = run_reduce_async(c);
+        if (rc) return rc;
+        CU(cudaStreamSynchronize(c->stream));
+        const uint32_t st = c->h_ctr->status;
+        if (!(st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull | kStatusBlobFull))) {
+            c->stage = 2;
+            return LOCUST_OK;
+        }
+        if (c->shuffled) return fail(c, LOCUST_E_CAPACITY, "table too small for merged partials; raise table_log2");
+        if (st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull)) {
+            uint64_t slots = c->slots, long_cap = c->long_cap;
+            if (st & kStatusTableFull) slots *= 4;
+            if (st & kStatusLongFull) { long_cap = c->h_ctr->n_long + (c->h_ctr->n_long >> 3) + 1024; }
+            if ((st & kStatusEntryFull) && !(st & (kStatusTableFull | kStatusLongFull))) slots *= 2;
+            if (slots > (1ull << 32)) return fail(c, LOCUST_E_CAPACITY, "combiner table would exceed 2^32 slots");
+            rc = alloc_sized(c, slots, long_cap);
+            if (rc) return rc;
+        } else {   // only the key blob was too small
+            cudaFree(c->red.key_blob); c->red.key_blob = nullptr;
+            c->red.blob_cap = c->h_ctr->blob_bytes + 64;
+            CU(dalloc(&c->red.key_blob, c->red.blob_cap));
+        }
+        // redo from the inputs
+        rc = clear_job(c);
+        if (rc) return rc;
+        CU(cudaEventRecord(c->ev[0], c->stream));
+        for (const auto &s : c->segments) { rc = run_map_segment(c, s); if (rc) return rc; }
+        CU(cudaEventRecord(c->ev[1], c->stream));
+        rc = run_process(c);
+        if (rc) return rc;
+    }
+    return fail(c, LOCUST_E_CAPACITY, "buffers still too small after repeated growth");
+}
+
+int ensure_host_result(locust_ctx *c) {
+    if (c->host_valid) return LOCUST_OK;
+    const uint64_t n = c->h_ctr->n_out, blob = c->h_ctr->blob_bytes;
+    if (n + 1 > c->h_rec_cap) {
+        cudaFreeHost(c->h_offsets); cudaFreeHost(c->h_counts); cudaFreeHost(c->h_vals);
+        c->h_offsets = c->h_counts = c->h_vals = nullptr;
+        c->h_rec_cap = n + 1 + (n >> 2);
+        CU(cudaMallocHost(reinterpret_cast<void **>(&c->h_offsets), c->h_rec_cap * 8));
+        CU(cudaMallocHost(reinterpret_cast<void **>(&c->h_counts), c->h_rec_cap * 8));
+        CU(cudaMallocHost(reinterpret_cast<void **>(&c->h_vals), c->h_rec_cap * 8));
+    }
+    if (blob + 1 > c->h_blob_cap) {
+        cudaFreeHost(c->h_blob); c->h_blob = nullptr;
+        c->h_blob_cap = blob + 1 + (blob >> 2);
+        CU(cudaMallocHost(reinterpret_cast<void **>(&c->h_blob), c->h_blob_cap));
+    }
+    CU(cudaMemcpyAsync(c->h_offsets, c->red.key_offsets, (n + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
+    if (n) {
+        CU(cudaMemcpyAsync(c->h_counts, c->red.counts, n * 8, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(c->h_vals, c->red.vals, n * 8, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (blob) CU(cudaMemcpyAsync(c->h_blob, c->red.key_blob, blob, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->host_valid = true;
+    return LOCUST_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *locust_version(void) { return "locust-b200 0.1 (sm_100a)"; }
+
+int locust_create(const locust_config *cfg, locust_ctx **out) {
+    if (!out) return LOCUST_E_ARG;
+    *out = nullptr;
+    locust_config def{};
+    if (!cfg) cfg = &def;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return LOCUST_E_CUDA;     // no CPU fallback, by design
+    if (cfg->device < 0 || cfg->device >= ndev) return LOCUST_E_ARG;
+    if (cfg->table_log2 > 32) return LOCUST_E_ARG;
+    locust_ctx *c = new (std::nothrow) locust_ctx();
+    if (!c) return LOCUST_E_NOMEM;
+    *out = c;                      // handed out even on failure so last_error can be read; destroy frees it
+    c->device = cfg->device;
+    c->flags = cfg->flags;
+    CU(cudaSetDevice(c->device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, c->device));
+    if (prop.major < 10) return fail(c, LOCUST_E_CUDA, "device is not sm_100 class (this library is built for sm_100a only)");
+    c->num_sms = prop.multiProcessorCount;
+    if (cfg->stream) c->stream = static_cast<cudaStream_t>(cfg->stream);
+    else { CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)); c->own_stream = true; }
+    CU(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    for (auto &ev : c->ev) CU(cudaEventCreate(&ev));
+    CU(map_kernel_setup());
+    CU(dalloc(&c->ctr, 1));
+    CU(cudaMallocHost(reinterpret_cast<void **>(&c->h_ctr), sizeof(Counters)));
+    memset(c->h_ctr, 0, sizeof(Counters));
+    CU(dalloc(&c->sort.hist, 16 * 256));
+    CU(dalloc(&c->sort.bases, 16 * 256));
+    CU(dalloc(&c->sort.tickets, 64));
+    CU(cudaMemsetAsync(c->sort.tickets, 0, 64 * sizeof(uint32_t), c->stream));
+    const uint32_t lg = cfg->table_log2 ? cfg->table_log2 : 20;
+    const uint64_t long_cap = cfg->long_capacity ? cfg->long_capacity : (1ull << 20);
+    int rc = alloc_sized(c, 1ull << lg, long_cap);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(c->stream));
+    return LOCUST_OK;
+}
+
+int locust_destroy(locust_ctx *c) {
+    if (!c) return LOCUST_E_ARG;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    drop_segments(c);
+    cudaFree(c->table); cudaFree(c->long_list); cudaFree(c->ctr);
+    free_record_buffers(c);
+    cudaFree(c->sort.hist); cudaFree(c->sort.bases); cudaFree(c->sort.tickets);
+    cudaFree(c->line_off); cudaFree(c->d_text); cudaFree(c->part_counts);
+    cudaFreeHost(c->h_ctr); cudaFreeHost(c->h_blob); cudaFreeHost(c->h_offsets);
+    cudaFreeHost(c->h_counts); cudaFreeHost(c->h_vals); cudaFreeHost(c->h_text);
+    for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return LOCUST_OK;
+}
+
+int locust_reset(locust_ctx *c) {
+    if (!c) return LOCUST_E_ARG;
+    CU(cudaSetDevice(c->device));
+    // device copies of host inputs may still be read by queued kernels
+    if (!c->segments.empty()) CU(cudaStreamSynchronize(c->stream));
+    drop_segments(c);
+    c->cleared = false;
+    c->shuffled = false;
+    c->stage = 0;
+    c->host_valid = false;
+    for (auto &b : c->ev_set) b = false;
+    c->launches = 0;
+    c->err.clear();
+    return LOCUST_OK;
+}
+
+int locust_map(locust_ctx *c, const void *data, uint64_t nbytes, int where) {
+    if (!c) return LOCUST_E_ARG;
+    if (!data && nbytes) return fail(c, LOCUST_E_ARG, "locust_map: data is NULL");
+    if (where != LOCUST_HOST && where != LOCUST_DEVICE) return fail(c, LOCUST_E_ARG, "locust_map: bad location");
+    if (c->stage != 0) return fail(c, LOCUST_E_STATE, "locust_map after locust_process; call locust_reset first");
+    CU(cudaSetDevice(c->device));
+    if (!c->cleared) {
+        CU(cudaEventRecord(c->ev[0], c->stream)); c->ev_set[0] = true;
+        int rc = clear_job(c);
+        if (rc) return rc;
+    }
+    int rc = LOCUST_OK;
+    if (nbytes) {
+        if (where == LOCUST_DEVICE) {
+            Segment s{static_cast<const uint8_t *>(data), nbytes, nullptr};
+            c->segments.push_back(s);
+            rc = run_map_segment(c, s);
+        } else {
+            uint8_t *dev = nullptr;
+            CU(cudaMalloc(reinterpret_cast<void **>(&dev), nbytes + 64));
+            c->segments.push_back(Segment{dev, nbytes, dev});
+            rc = map_host(c, static_cast<const uint8_t *>(data), nbytes, dev);
+        }
+    }
+    if (rc) return rc;
+    CU(cudaEventRecord(c->ev[1], c->stream)); c->ev_set[1] = true;
+    return LOCUST_OK;
+}
+
+int locust_process(locust_ctx *c) {
+    if (!c) return LOCUST_E_ARG;
+    if (c->stage != 0) return fail(c, LOCUST_E_STATE, "locust_process called twice");
+    CU(cudaSetDevice(c->device));
+    if (!c->cleared) {            // no input at all: still a valid, empty job
+        CU(cudaEventRecord(c->ev[0], c->stream)); c->ev_set[0] = true;
+        int rc = clear_job(c);
+        if (rc) return rc;
+        CU(cudaEventRecord(c->ev[1], c->stream)); c->ev_set[1] = true;
+    }
+    return run_process(c);
+}
+
+int locust_reduce(locust_ctx *c) {
+    if (!c) return LOCUST_E_ARG;
+    if (c->stage != 1) return fail(c, LOCUST_E_STATE, "locust_reduce needs locust_process first");
+    CU(cudaSetDevice(c->device));
+    return finish_reduce(c);
+}
+
+int locust_wordcount(locust_ctx *c, const void *data, uint64_t nbytes, int where) {
+    int rc = locust_reset(c);
+    if (rc) return rc;
+    rc = locust_map(c, data, nbytes, where);
+    if (rc) return rc;
+    rc = locust_process(c);
+    if (rc) return rc;
+    return locust_reduce(c);
+}
+
+int locust_result_device(locust_ctx *c, const uint8_t **key_blob, const uint64_t **key_offsets,
+                         const uint64_t **counts, const uint64_t **vals, uint64_t *n) {
+    if (!c) return LOCUST_E_ARG;
+    if (c->stage != 2) return fail(c, LOCUST_E_STATE, "no result yet: run locust_reduce");
+    if (key_blob) *key_blob = c->red.key_blob;
+    if (key_offsets) *key_offsets = c->red.key_offsets;
+    if (counts) *counts = reinterpret_cast<const uint64_t *>(c->red.counts);
+    if (vals) *vals = reinterpret_cast<const uint64_t *>(c->red.vals);
+    if (n) *n = c->h_ctr->n_out;
+    return LOCUST_OK;
+}
+
+int locust_result_host(locust_ctx *c, const uint8_t **key_blob, const uint64_t **key_offsets,
+                       const uint64_t **counts, const uint64_t **vals, uint64_t *n) {
+    if (!c) return LOCUST_E_ARG;
+    if (c->stage != 2) return fail(c, LOCUST_E_STATE, "no result yet: run locust_reduce");
+    CU(cudaSetDevice(c->device));
+    int rc = ensure_host_result(c);
+    if (rc) return rc;
+    if (key_blob) *key_blob = c->h_blob;
+    if (key_offsets) *key_offsets = c->h_offsets;
+    if (counts) *counts = c->h_counts;
+    if (vals) *vals = c->h_vals;
+    if (n) *n = c->h_ctr->n_out;
+    return LOCUST_OK;
+}
+
+int locust_format_result(locust_ctx *c, int cpu_format, const char **text, uint64_t *nbytes) {
+    if (!c || !text || !nbytes) return LOCUST_E_ARG;
+    if (c->stage != 2) return fail(c, LOCUST_E_STATE, "no result yet: run locust_reduce");
+    CU(cudaSetDevice(c->device));
+    const uint64_t n = c->h_ctr->n_out;
+    if (n + 1 > c->line_cap) {
+        cudaFree(c->line_off); c->line_off = nullptr;
+        c->line_cap = n + 1;
+        CU(dalloc(&c->line_off, c->line_cap));
+    }
+    c->launches += (uint64_t)launch_format_sizes(c->red, c->ctr, cpu_format, c->line_off, c->sort, take_epochs(c, 1),
+                                                 c->num_sms, c->stream);
+    CU(cudaMemcpyAsync(c->h_ctr, c->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    const uint64_t tb = c->h_ctr->text_bytes;
+    if (tb + 1 > c->d_text_cap) {
+        cudaFree(c->d_text); c->d_text = nullptr;
+        c->d_text_cap = tb + 1;
+        CU(dalloc(&c->d_text, c->d_text_cap));
+    }
+    if (tb + 1 > c->h_text_cap) {
+        cudaFreeHost(c->h_text); c->h_text = nullptr;
+        c->h_text_cap = tb + 1;
+        CU(cudaMallocHost(reinterpret_cast<void **>(&c->h_text), c->h_text_cap));
+    }
+    c->launches += (uint64_t)launch_format_write(c->red, c->ctr, cpu_format, c->line_off, c->d_text, c->d_text_cap,
+                                                 c->num_sms, c->stream);
+    CU(cudaGetLastError());
+    if (tb) CU(cudaMemcpyAsync(c->h_text, c->d_text, tb, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    *text = c->h_text;
+    *nbytes = tb;
+    return LOCUST_OK;
+}
+
+float locust_stage_ms(locust_ctx *c, int stage) {
+    if (!c || stage < 0 || stage > 2) return -1.0f;
+    if (!c->ev_set[2 * stage] || !c->ev_set[2 * stage + 1]) return -1.0f;
+    cudaSetDevice(c->device);
+    if (cudaEventSynchronize(c->ev[2 * stage + 1]) != cudaSuccess) return -1.0f;
+    float ms = -1.0f;
+    if (cudaEventElapsedTime(&ms, c->ev[2 * stage], c->ev[2 * stage + 1]) != cudaSuccess) return -1.0f;
+    return ms;
+}
+
+int locust_stats(locust_ctx *c, uint64_t *tokens, uint64_t *unique_keys, uint64_t *kernel_launches) {
+    if (!c) return LOCUST_E_ARG;
+    if (tokens) *tokens = c->stage == 2 ? c->h_ctr->total : 0;
+    if (unique_keys) *unique_keys = c->stage == 2 ? c->h_ctr->n_out : 0;
+    if (kernel_launches) *kernel_launches = c->launches;
+    return LOCUST_OK;
+}
+
+const char *locust_last_error(locust_ctx *c) { return c ? c->err.c_str() : "null context"; }
+
+// ---- multi-GPU shuffle ------------------------------------------------------------------
+int locust_shuffle_sizes(locust_ctx *c, uint32_t nparts, uint64_t *bytes_per_part) {
+    if (!c || !bytes_per_part || nparts == 0) return LOCUST_E_ARG;
+    return fail(c, LOCUST_E_STATE, "shuffle not built yet");
+}
+int locust_shuffle_pack(locust_ctx *c, uint32_t nparts, void *dev_out, const uint64_t *part_offsets) {
+    if (!c || !dev_out || !part_offsets || nparts == 0) return LOCUST_E_ARG;
+    return fail(c, LOCUST_E_STATE, "shuffle not built yet");
+}
+int locust_shuffle_begin_merge(locust_ctx *c) {
+    if (!c) return LOCUST_E_ARG;
+    return fail(c, LOCUST_E_STATE, "shuffle not built yet");
+}
+int locust_shuffle_merge(locust_ctx *c, const void *dev_records, uint64_t nbytes) {
+    if (!c || (!dev_records && nbytes)) return LOCUST_E_ARG;
+    return fail(c, LOCUST_E_STATE, "shuffle not built yet");
+}
+
+}  // extern "C"

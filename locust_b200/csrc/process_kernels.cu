@@ -1,0 +1,297 @@
+// process_kernels.cu -- PROCESS stage: compaction of the combined records out of
+// the hash table and their lexicographic sort.
+//
+// Stands in for thrust::partition(KeyIntValueNotEmpty) + thrust::sort(KIVComparator)
+// (MapReduce/src/main.cu:411-415; KeyValue.h:20-33, :79-84).  The sort is a
+// hand-written onesweep LSD radix sort (8-bit digits, decoupled look-back, one
+// kernel per digit that moves data) over the 16-byte big-endian key prefix; keys
+// longer than 16 bytes are put in order afterwards by full comparison inside
+// their run of equal prefixes.
+#include "kernels.cuh"
+#include "lookback.cuh"
+
+namespace locust {
+
+constexpr uint32_t kFull = 0xFFFFFFFFu;
+
+LC_D uint32_t key_len16(uint64_t k0, uint64_t k1) {
+    // number of non-zero bytes of the zero padded little-endian key
+    return k1 ? 16u - (uint32_t)(__clzll((long long)k1) >> 3) : 8u - (uint32_t)(__clzll((long long)k0) >> 3);
+}
+
+// ---- extract ------------------------------------------------------------------
+__global__ void __launch_bounds__(256) extract_kernel(const Slot *__restrict__ table, uint64_t slots, Records r,
+                                                      Counters *ctr) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t rounds = (slots + stride - 1) / stride;
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (uint64_t it = 0; it < rounds; ++it, i += stride) {
+        ulonglong2 k = make_ulonglong2(0ull, 0ull);
+        unsigned long long cnt = 0;
+        if (i < slots) {
+            const ulonglong4 v = *reinterpret_cast<const ulonglong4 *>(table + i);
+            k.x = v.x; k.y = v.y; cnt = v.z;
+        }
+        const bool occ = (k.x | k.y) != 0ull;
+        const uint32_t m = __ballot_sync(kFull, occ);
+        if (m == 0u) continue;
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(&ctr->n_entries, (unsigned long long)__popc(m));
+        base = __shfl_sync(kFull, base, 0);
+        if (occ) {
+            const unsigned long long e = base + __popc(m & ((1u << lane) - 1u));
+            if (e < r.cap) {
+                r.a0[e] = bswap64(k.x);
+                r.a1[e] = bswap64(k.y);
+                r.ia[e] = (uint32_t)e;
+                r.count[e] = cnt;
+                r.ref[e].ptr = nullptr;
+                r.ref[e].len = key_len16(k.x, k.y);
+            } else {
+                atomicOr(&ctr->status, kStatusEntryFull);
+            }
+        }
+    }
+}
+
+// every occurrence of a long token becomes a record with count 1; REDUCE merges them
+__global__ void __launch_bounds__(256) append_long_kernel(const LongTok *__restrict__ list, uint64_t long_cap,
+                                                          Records r, Counters *ctr) {
+    unsigned long long n = ctr->n_long;
+    if (n > long_cap) n = long_cap;
+    const unsigned long long base = ctr->n_entries;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned long long e = base + i;
+        if (e >= r.cap) { atomicOr(&ctr->status, kStatusEntryFull); continue; }
+        const LongTok t = list[i];
+        uint64_t b0 = 0, b1 = 0;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+            b0 = (b0 << 8) | t.ptr[b];
+            b1 = (b1 << 8) | t.ptr[8 + b];
+        }
+        r.a0[e] = b0; r.a1[e] = b1; r.ia[e] = (uint32_t)e;
+        r.count[e] = 1ull;
+        r.ref[e] = t;
+    }
+}
+__global__ void bump_entries_kernel(uint64_t long_cap, uint64_t cap, Counters *ctr) {
+    unsigned long long n = ctr->n_long;
+    if (n > long_cap) n = long_cap;
+    unsigned long long e = ctr->n_entries + n;
+    if (e > cap) e = cap;
+    ctr->n_entries = e;
+}
+
+// ---- radix sort -----------------------------------------------------------------
+LC_D uint32_t digit_of(uint64_t be0, uint64_t be1, int pass) {
+    return pass < 8 ? (uint32_t)(be1 >> (8 * pass)) & 0xFFu : (uint32_t)(be0 >> (8 * (pass - 8))) & 0xFFu;
+}
+
+__global__ void __launch_bounds__(256) sort_hist_kernel(Records r, const Counters *ctr, uint32_t *hist) {
+    __shared__ uint32_t sh[16 * 256];
+    for (int i = threadIdx.x; i < 16 * 256; i += 256) sh[i] = 0u;
+    __syncthreads();
+    const unsigned long long n = ctr->n_entries;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * 256 + threadIdx.x; i < n;
+         i += (unsigned long long)gridDim.x * 256) {
+        const uint64_t k0 = r.a0[i], k1 = r.a1[i];
+#pragma unroll
+        for (int p = 0; p < 16; ++p) atomicAdd(&sh[p * 256 + digit_of(k0, k1, p)], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 16 * 256; i += 256)
+        if (sh[i]) atomicAdd(&hist[i], sh[i]);
+}
+
+// one block: per digit position, bucket bases and whether the pass moves anything
+__global__ void __launch_bounds__(256) sort_prep_kernel(const uint32_t *hist, uint32_t *bases, Counters *ctr) {
+    __shared__ uint32_t warp_tot[8];
+    __shared__ uint32_t uniform;
+    const uint32_t d = threadIdx.x, lane = d & 31u, w = d >> 5;
+    const unsigned long long n = ctr->n_entries;
+    uint32_t parity = 0;
+    for (int p = 0; p < 16; ++p) {
+        if (d == 0) uniform = 0u;
+        __syncthreads();
+        const uint32_t v = hist[p * 256 + d];
+        if ((unsigned long long)v == n) uniform = 1u;       // every key has this digit (also n == 0)
+        uint32_t x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(kFull, x, o);
+            if (lane >= (uint32_t)o) x += y;
+        }
+        if (lane == 31) warp_tot[w] = x;
+        __syncthreads();
+        uint32_t off = 0;
+        for (uint32_t k = 0; k < w; ++k) off += warp_tot[k];
+        bases[p * 256 + d] = off + x - v;
+        const uint32_t active = uniform ? 0u : 1u;
+        if (d == 0) { ctr->pass_active[p] = active; ctr->pass_src[p] = parity; }
+        parity ^= active;
+        __syncthreads();
+    }
+    if (d == 0) ctr->sort_parity = parity;
+}
+
+// One LSD pass, onesweep style: a tile of 2048 records is ranked in registers
+// (warp match + per-warp digit counters), its digit totals are chained to the
+// previous tiles' by decoupled look-back, and the records are scattered to their
+// final place for this digit.  Stable.
+__global__ void __launch_bounds__(256) sort_pass_kernel(Records r, const uint32_t *__restrict__ bases,
+                                                        const Counters *ctr, int pass, uint64_t *lb_state,
+                                                        uint32_t *ticket, uint32_t epoch) {
+    if (!ctr->pass_active[pass]) return;
+    __shared__ uint32_t wcnt[8][256];
+    __shared__ uint32_t tile_base[256];
+    __shared__ uint32_t tslot;
+    const unsigned long long n = ctr->n_entries;
+    const uint32_t ntiles = (uint32_t)((n + kSortTile - 1) / kSortTile);
+    const bool from_b = ctr->pass_src[pass] != 0u;
+    const uint64_t *s0 = from_b ? r.b0 : r.a0, *s1 = from_b ? r.b1 : r.a1;
+    const uint32_t *si = from_b ? r.ib : r.ia;
+    uint64_t *d0 = from_b ? r.a0 : r.b0, *d1 = from_b ? r.a1 : r.b1;
+    uint32_t *di = from_b ? r.ia : r.ib;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, w = tid >> 5;
+
+    for (;;) {
+        const uint32_t tile = take_ticket(ticket, &tslot);
+        if (tile >= ntiles) break;
+        for (int i = tid; i < 8 * 256; i += 256) (&wcnt[0][0])[i] = 0u;
+        __syncthreads();
+        uint64_t k0[8], k1[8];
+        uint32_t ix[8], dg[8], rk[8];
+        const unsigned long long tbase = (unsigned long long)tile * kSortTile + w * 256u + lane;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const unsigned long long e = tbase + i * 32u;
+            const bool valid = e < n;
+            k0[i] = valid ? s0[e] : 0ull;
+            k1[i] = valid ? s1[e] : 0ull;
+            ix[i] = valid ? si[e] : 0u;
+            dg[i] = valid ? digit_of(k0[i], k1[i], pass) : 0x100u;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t peers = __match_any_sync(kFull, dg[i]);
+            const uint32_t leader = (uint32_t)__ffs((int)peers) - 1u;
+            uint32_t base = 0;
+            if (lane == leader && dg[i] < 256u) {
+                base = wcnt[w][dg[i]];
+                wcnt[w][dg[i]] = base + (uint32_t)__popc(peers);
+            }
+            base = __shfl_sync(kFull, base, leader);
+            rk[i] = base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
+            __syncwarp();
+        }
+        __syncthreads();
+        {   // thread = digit: offsets of each warp's records inside the tile, tile total
+            uint32_t tot = 0;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { const uint32_t c = wcnt[k][tid]; wcnt[k][tid] = tot; tot += c; }
+            uint64_t *st = lb_state + (uint64_t)tile * 256u + tid;
+            uint64_t prefix = 0;
+            if (tile == 0) {
+                lb_store(st, lb_pack(epoch, kLbInclusive, tot));
+            } else {
+                lb_store(st, lb_pack(epoch, kLbAggregate, tot));
+                prefix = lb_lookback(lb_state, tile, 256u, tid, epoch);
+                lb_store(st, lb_pack(epoch, kLbInclusive, prefix + tot));
+            }
+            tile_base[tid] = bases[pass * 256 + tid] + (uint32_t)prefix;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if (dg[i] < 256u) {
+                const uint32_t pos = tile_base[dg[i]] + wcnt[w][dg[i]] + rk[i];
+                d0[pos] = k0[i]; d1[pos] = k1[i]; di[pos] = ix[i];
+            }
+        }
+        __syncthreads();
+    }
+    return_ticket(ticket);
+}
+
+// ---- keys longer than 16 bytes ---------------------------------------------------
+// order of two keys that agree on their first 16 bytes
+LC_D int cmp_tail(const LongTok &a, const LongTok &b) {
+    const uint64_t la = a.len, lb = b.len;
+    const uint64_t m = la < lb ? la : lb;
+    for (uint64_t i = 16; i < m; ++i) {
+        const uint32_t x = a.ptr[i], y = b.ptr[i];
+        if (x != y) return x < y ? -1 : 1;
+    }
+    return la < lb ? -1 : (la > lb ? 1 : 0);
+}
+
+// A run of records with equal 16-byte prefix that holds keys of more than 16
+// bytes is put in full-key order by the thread that owns the run's first record.
+__global__ void __launch_bounds__(256) tie_fix_kernel(Records r, const Counters *ctr) {
+    const unsigned long long n = ctr->n_entries;
+    const bool in_b = ctr->sort_parity != 0u;
+    const uint64_t *s0 = in_b ? r.b0 : r.a0, *s1 = in_b ? r.b1 : r.a1;
+    uint32_t *si = in_b ? r.ib : r.ia;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i + 1 < n;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const uint64_t a = s0[i], b = s1[i];
+        if ((b & 0xFFull) == 0ull) continue;                          // key shorter than 16 bytes
+        if (i > 0 && s0[i - 1] == a && s1[i - 1] == b) continue;      // not the first of its run
+        if (s0[i + 1] != a || s1[i + 1] != b) continue;               // run of one
+        unsigned long long j = i + 2;
+        while (j < n && s0[j] == a && s1[j] == b) ++j;
+        // insertion sort of si[i..j) by full key
+        for (unsigned long long x = i + 1; x < j; ++x) {
+            const uint32_t v = si[x];
+            const LongTok tv = r.ref[v];
+            unsigned long long y = x;
+            while (y > i) {
+                const uint32_t u = si[y - 1];
+                if (cmp_tail(r.ref[u], tv) <= 0) break;
+                si[y] = u; --y;
+            }
+            si[y] = v;
+        }
+    }
+}
+
+// ---- host launchers -----------------------------------------------------------------
+static inline unsigned grid_for(uint64_t n, unsigned per_block, int num_sms, int blocks_per_sm) {
+    uint64_t g = (n + per_block - 1) / per_block;
+    const uint64_t cap = (uint64_t)num_sms * blocks_per_sm;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (unsigned)g;
+}
+
+int launch_extract(const Slot *table, uint64_t slots, Records r, Counters *ctr, int num_sms, cudaStream_t st) {
+    extract_kernel<<<grid_for(slots, 256 * 4, num_sms, 8), 256, 0, st>>>(table, slots, r, ctr);
+    return 1;
+}
+
+int launch_append_long(const LongTok *list, uint64_t long_cap, Records r, Counters *ctr, int num_sms,
+                       cudaStream_t st) {
+    append_long_kernel<<<grid_for(long_cap, 256, num_sms, 4), 256, 0, st>>>(list, long_cap, r, ctr);
+    bump_entries_kernel<<<1, 1, 0, st>>>(long_cap, r.cap, ctr);
+    return 2;
+}
+
+int launch_sort_records(Records r, SortScratch s, Counters *ctr, uint32_t epoch, int num_sms, cudaStream_t st) {
+    cudaMemsetAsync(s.hist, 0, 16 * 256 * sizeof(uint32_t), st);
+    sort_hist_kernel<<<grid_for(r.cap, 256 * 8, num_sms, 4), 256, 0, st>>>(r, ctr, s.hist);
+    sort_prep_kernel<<<1, 256, 0, st>>>(s.hist, s.bases, ctr);
+    const unsigned g = grid_for(r.cap, kSortTile, num_sms, 4);
+    for (int p = 0; p < 16; ++p)
+        sort_pass_kernel<<<g, 256, 0, st>>>(r, s.bases, ctr, p, s.lb_state, s.tickets + 2 * p, epoch + (uint32_t)p);
+    return 18;
+}
+
+int launch_tie_fix(Records r, Counters *ctr, int num_sms, cudaStream_t st) {
+    tie_fix_kernel<<<grid_for(r.cap, 256, num_sms, 8), 256, 0, st>>>(r, ctr);
+    return 1;
+}
+
+}  // namespace locust
