@@ -61,7 +61,10 @@ LC_HD uint32_t classify16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
 
 LC_HD uint32_t byte_perm(uint32_t a, uint32_t b, uint32_t s) {
 #if defined(__CUDA_ARCH__)
-    return __byte_perm(a, b, s);
+    // raw PRMT: the __byte_perm intrinsic only honours three bits per selector nibble
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(s));
+    return r;
 #else
     // PTX prmt, default mode: nibble i of s picks one of the 8 bytes {a,b}; bit 3
     // of the nibble replicates that byte's sign bit instead.

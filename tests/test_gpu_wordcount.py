@@ -318,7 +318,7 @@ def test_cli_matches_reference_stdout(lb, tmp_path):
     # [line_start, line_end) window
     r = subprocess.run([exe, path, "10", "20"], capture_output=True, env=env, check=True).stdout
     with open(path, "rb") as f:
-        window = b"".join(f.read().split(b"\n")[10:20][i] + b"\n" for i in range(10))
+        window = b"".join(l + b"\n" for l in f.read().split(b"\n")[10:20])
     from oracle import pyoracle
     want = pyoracle.wordcount(window).cpu_lines
     got = b"".join(l + b"\n" for l in r.split(b"\n") if l.startswith(b"print key: "))
