@@ -93,6 +93,36 @@ LC_HD void extract_key8(uint32_t wa, uint32_t wb, uint32_t wc, uint32_t o, uint3
     hi = byte_perm(wb, wc, sel | (z >> 16));
 }
 
+// Key of a token of L <= 16 bytes starting at byte `o` (0..3) of word w0, with
+// w1..w4 the following words: four little-endian words, zero padded past L.
+// ASCII variant (every byte of the window < 0x80): bytes past L are zeroed inside
+// the PRMT by the sign-replicate bit, as in extract_key8.
+LC_HD void key_selectors(uint32_t o, uint32_t L, uint32_t &sel, uint32_t &zlo, uint32_t &zhi) {
+    sel = 0x3210u + 0x1111u * o;
+    zlo = (L >= 8u) ? 0u : (0x88888888u << (4u * L));
+    zhi = (L >= 16u) ? 0u : ((L >= 8u) ? (0x88888888u << (4u * (L - 8u))) : 0x88888888u);
+}
+LC_HD void extract_key16_ascii(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32_t w4, uint32_t o,
+                               uint32_t L, uint32_t &a, uint32_t &b, uint32_t &c, uint32_t &d) {
+    uint32_t sel, zlo, zhi;
+    key_selectors(o, L, sel, zlo, zhi);
+    a = byte_perm(w0, w1, sel | (zlo & 0xFFFFu));
+    b = byte_perm(w1, w2, sel | (zlo >> 16));
+    c = byte_perm(w2, w3, sel | (zhi & 0xFFFFu));
+    d = byte_perm(w3, w4, sel | (zhi >> 16));
+}
+// Any byte values: align with PRMT, then AND with a byte mask built from the same
+// nibble mask (nibble 8 -> selector 1 -> byte 0x00; nibble 0 -> selector 0 -> 0xFF).
+LC_HD void extract_key16_any(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32_t w4, uint32_t o,
+                             uint32_t L, uint32_t &a, uint32_t &b, uint32_t &c, uint32_t &d) {
+    uint32_t sel, zlo, zhi;
+    key_selectors(o, L, sel, zlo, zhi);
+    a = byte_perm(w0, w1, sel) & byte_perm(0xFFu, 0u, (zlo >> 3) & 0xFFFFu);
+    b = byte_perm(w1, w2, sel) & byte_perm(0xFFu, 0u, zlo >> 19);
+    c = byte_perm(w2, w3, sel) & byte_perm(0xFFu, 0u, (zhi >> 3) & 0xFFFFu);
+    d = byte_perm(w3, w4, sel) & byte_perm(0xFFu, 0u, zhi >> 19);
+}
+
 // Index of the lowest set bit of a 4-bit value (0 for 0), from a 32-bit table.
 LC_HD uint32_t low_bit4(uint32_t n) { return (0x12131210u >> (2u * n)) & 3u; }
 

@@ -21,8 +21,9 @@ namespace locust {
 
 constexpr int kLogSmemSlots = 14;
 constexpr uint32_t kSmemSlots = 1u << kLogSmemSlots;
-constexpr uint32_t kSmemBytes = kSmemSlots * (8 + 4);
+constexpr uint32_t kQueueSlots = 64;             // per warp, 16 bytes each
 constexpr int kMapThreads = 1024;
+constexpr uint32_t kSmemBytes = kSmemSlots * (8 + 4) + (kMapThreads / 32) * kQueueSlots * 16;
 constexpr uint32_t kFull = 0xFFFFFFFFu;
 constexpr uint32_t kMaxProbe = 1u << 14;
 
@@ -130,6 +131,90 @@ LC_D uint4 load_chunk(const MapParams &p, uint64_t row, uint32_t lane) {
     return v;
 }
 
+// Per-warp state of the combiner: the CTA's shared table and this warp's queue of
+// keys that have to go to the global table.  Deferring them costs a few
+// instructions per step; inserting them one batch of 32 at a time keeps every lane
+// busy in the long global-insert code instead of one or two.
+struct WarpCtx {
+    uint64_t *skeys;
+    uint32_t *scnt;
+    ulonglong2 *queue;     // kQueueSlots entries, this warp's
+    uint32_t qn;           // entries queued (warp-uniform)
+    uint32_t lane;
+    bool use_smem;
+};
+
+LC_D void drain_queue(const MapParams &p, WarpCtx &wc, uint32_t keep_below) {
+    // pops batches of up to 32 keys until fewer than keep_below remain
+    while (wc.qn >= keep_below && wc.qn > 0u) {
+        __syncwarp();
+        const uint32_t take = wc.qn < 32u ? wc.qn : 32u;
+        if (wc.lane < take) {
+            const ulonglong2 k = wc.queue[wc.qn - take + wc.lane];
+            global_insert(p, k.x, k.y, 1ull);
+        }
+        wc.qn -= take;
+        __syncwarp();
+    }
+}
+
+// All lanes call this together.  `has` marks the lanes that hold a token of L <= 16
+// bytes whose bytes start at byte `o` of w0.  Short tokens are counted in the shared
+// table; misses and tokens of 9..16 bytes are queued for the global table.
+template <bool ASCII>
+LC_D void handle_token(const MapParams &p, WarpCtx &wc, bool has, uint32_t o, uint32_t L, uint32_t w0, uint32_t w1,
+                       uint32_t w2, uint32_t w3, uint32_t w4) {
+    uint32_t a = 0, b = 0, c = 0, d = 0;
+    bool defer = false;
+    if (has) {
+        if (ASCII) extract_key16_ascii(w0, w1, w2, w3, w4, o, L, a, b, c, d);
+        else extract_key16_any(w0, w1, w2, w3, w4, o, L, a, b, c, d);
+        defer = !(L <= 8u && wc.use_smem && smem_insert(wc.skeys, wc.scnt, a, b));
+    }
+    const uint32_t m = __ballot_sync(kFull, defer);
+    if (m) {
+        if (defer)
+            wc.queue[wc.qn + __popc(m & ((1u << wc.lane) - 1u))] =
+                make_ulonglong2((uint64_t)a | ((uint64_t)b << 32), (uint64_t)c | ((uint64_t)d << 32));
+        wc.qn += __popc(m);
+        if (wc.qn >= 32u) drain_queue(p, wc, 32u);
+    }
+}
+
+template <bool ASCII>
+LC_D void tokenise_row(const MapParams &p, WarpCtx &wc, const uint32_t (&w)[8], uint32_t starts, uint32_t dd,
+                       uint64_t chunk_pos) {
+    uint32_t rem = starts;
+    // first token of each 4-byte word: register indices are static
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const uint32_t sj = (starts >> (4 * j)) & 0xFu;
+        const uint32_t o = low_bit4(sj);
+        const uint32_t pp = 4 * j + o;
+        const uint32_t L = (uint32_t)__ffs((int)(dd >> pp)) - 1u;            // no delimiter in the window -> huge
+        const bool has = sj != 0u && L <= 16u;
+        if (has) rem &= ~(1u << pp);
+        handle_token<ASCII>(p, wc, has, o, L, w[j], w[j + 1], w[j + 2], w[j + 3], w[j + 4]);
+    }
+    // what is left: second tokens of a word (dynamic word index) and tokens that leave the window
+    while (__any_sync(kFull, rem != 0u)) {
+        const uint32_t pp = rem ? (uint32_t)__ffs((int)rem) - 1u : 0u;
+        const uint32_t L = (uint32_t)__ffs((int)(dd >> pp)) - 1u;
+        const bool has = rem != 0u && L <= 16u;
+        const bool far = rem != 0u && L > 16u;
+        rem &= rem - 1u;
+        const uint32_t j = pp >> 2;
+        const uint32_t t0 = (j & 1u) ? w[1] : w[0], t1 = (j & 1u) ? w[2] : w[1], t2 = (j & 1u) ? w[3] : w[2],
+                       t3 = (j & 1u) ? w[4] : w[3], t4 = (j & 1u) ? w[5] : w[4], t5 = (j & 1u) ? w[6] : w[5],
+                       t6 = (j & 1u) ? w[7] : w[6];
+        const uint32_t v0 = (j & 2u) ? t2 : t0, v1 = (j & 2u) ? t3 : t1, v2 = (j & 2u) ? t4 : t2,
+                       v3 = (j & 2u) ? t5 : t3, v4 = (j & 2u) ? t6 : t4;
+        handle_token<ASCII>(p, wc, has, pp & 3u, L, v0, v1, v2, v3, v4);
+        if (far) token_generic(p, wc.skeys, wc.scnt, chunk_pos + pp);
+        __syncwarp();
+    }
+}
+
 __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const __grid_constant__ MapParams p) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     uint64_t *skeys = reinterpret_cast<uint64_t *>(smem_raw);
@@ -143,7 +228,13 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
     const uint64_t nrows = (p.hi + 511ull) >> 9;
     const uint64_t r0 = nrows * gw / nwarps, r1 = nrows * (gw + 1) / nwarps;
     const bool use_fast = !(p.flags & LOCUST_F_GENERIC_TOKENISER);
-    const bool use_smem = !(p.flags & LOCUST_F_NO_SMEM_COMBINER);
+    WarpCtx wc;
+    wc.skeys = skeys;
+    wc.scnt = scnt;
+    wc.queue = reinterpret_cast<ulonglong2 *>(smem_raw + kSmemSlots * 12) + (threadIdx.x >> 5) * kQueueSlots;
+    wc.qn = 0u;
+    wc.lane = lane;
+    wc.use_smem = !(p.flags & LOCUST_F_NO_SMEM_COMBINER);
 
     if (r0 < r1) {
         uint4 c = load_chunk(p, r0, lane);
@@ -165,40 +256,31 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
             const uint32_t starts = ~dc & ((dc << 1) | (d_dn >> 15)) & 0xFFFFu;
             const uint32_t dd = dc | (d_up << 16);
             const uint64_t chunk_pos = row * 512ull + lane * 16u;
-            uint32_t rem = starts;
-            if (use_fast && asc_c && asc_n) {
-                uint32_t w[6];
+            if (use_fast) {
+                // 32-byte window: this lane's chunk and the next lane's (lane 31: next row's first chunk)
+                uint32_t w[8];
                 w[0] = c.x; w[1] = c.y; w[2] = c.z; w[3] = c.w;
                 w[4] = __shfl_sync(kFull, lane == 0 ? n.x : c.x, (lane + 1) & 31);
                 w[5] = __shfl_sync(kFull, lane == 0 ? n.y : c.y, (lane + 1) & 31);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const uint32_t sj = (starts >> (4 * j)) & 0xFu;
-                    if (sj) {
-                        const uint32_t o = low_bit4(sj);
-                        const uint32_t pp = 4 * j + o;
-                        const uint32_t y = dd >> pp;
-                        const uint32_t L = (uint32_t)__ffs((int)y) - 1u;     // y == 0 -> 0xFFFFFFFF
-                        if (L <= 8u) {
-                            rem &= ~(1u << pp);
-                            uint32_t lo, hi;
-                            extract_key8(w[j], w[j + 1], w[j + 2], o, L, lo, hi);
-                            if (!(use_smem && smem_insert(skeys, scnt, lo, hi)))
-                                global_insert(p, (uint64_t)lo | ((uint64_t)hi << 32), 0ull, 1ull);
-                        }
-                    }
+                w[6] = __shfl_sync(kFull, lane == 0 ? n.z : c.z, (lane + 1) & 31);
+                w[7] = __shfl_sync(kFull, lane == 0 ? n.w : c.w, (lane + 1) & 31);
+                if (asc_c && asc_n) tokenise_row<true>(p, wc, w, starts, dd, chunk_pos);
+                else tokenise_row<false>(p, wc, w, starts, dd, chunk_pos);
+            } else {
+                uint32_t rem = starts;
+                while (rem) {
+                    const uint32_t pp = (uint32_t)__ffs((int)rem) - 1u;
+                    rem &= rem - 1u;
+                    token_generic(p, skeys, scnt, chunk_pos + pp);
                 }
-            }
-            while (rem) {
-                const uint32_t pp = (uint32_t)__ffs((int)rem) - 1u;
-                rem &= rem - 1u;
-                token_generic(p, skeys, scnt, chunk_pos + pp);
+                __syncwarp();
             }
             pd = dc; c = n; dc = dn; asc_c = asc_n;
             n = nn;
             dn = classify16(n.x, n.y, n.z, n.w);
             asc_n = !__any_sync(kFull, (n.x | n.y | n.z | n.w) & 0x80808080u);
         }
+        drain_queue(p, wc, 1u);
     }
     __syncthreads();
     // flush the CTA's combiner into the global table

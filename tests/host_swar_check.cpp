@@ -54,6 +54,26 @@ int main() {
                 if ((((uint64_t)hi << 32) | lo) != want) { printf("extract_key8 o=%u L=%u\n", o, L); return 1; }
             }
     }
+    // extract_key16_*: all start offsets and lengths 1..16; the ASCII variant on ASCII data,
+    // the general variant on every byte value except NUL
+    for (int t = 0; t < 60000; ++t) {
+        uint8_t b[20], g[20];
+        for (auto &x : b) x = (uint8_t)(1 + rnd() % 127);
+        for (auto &x : g) x = (uint8_t)(1 + rnd() % 255);
+        uint32_t w[5], v[5];
+        memcpy(w, b, 20);
+        memcpy(v, g, 20);
+        for (uint32_t o = 0; o < 4; ++o)
+            for (uint32_t L = 1; L <= 16; ++L) {
+                uint32_t k[4], q[4];
+                extract_key16_ascii(w[0], w[1], w[2], w[3], w[4], o, L, k[0], k[1], k[2], k[3]);
+                extract_key16_any(v[0], v[1], v[2], v[3], v[4], o, L, q[0], q[1], q[2], q[3]);
+                uint8_t want[16] = {0}, wantg[16] = {0};
+                for (uint32_t i = 0; i < L; ++i) { want[i] = b[o + i]; wantg[i] = g[o + i]; }
+                if (memcmp(k, want, 16) != 0) { printf("extract_key16_ascii o=%u L=%u\n", o, L); return 1; }
+                if (memcmp(q, wantg, 16) != 0) { printf("extract_key16_any o=%u L=%u\n", o, L); return 1; }
+            }
+    }
     for (uint32_t n = 1; n < 16; ++n)
         if (low_bit4(n) != (uint32_t)__builtin_ctz(n)) { printf("low_bit4 %u\n", n); return 1; }
     if (bswap64(0x0102030405060708ull) != 0x0807060504030201ull) { printf("bswap64\n"); return 1; }
