@@ -148,6 +148,45 @@ int locust_shuffle_begin_merge(locust_ctx *ctx);
  * locust_reduce has returned). */
 int locust_shuffle_merge(locust_ctx *ctx, const void *dev_records, uint64_t nbytes);
 
+/* ---- for callers that cannot allocate ------------------------------------------
+ * No counterpart in the reference (its main() allocates freely, main.cu:393,:402,:451).
+ *
+ * locust_count_static runs the MAP stage -- tokenise and combine (word, 1) pairs,
+ * exactly as locust_map does -- without calling cudaMalloc, cudaFree or any other
+ * allocating routine.  It exists for hosts that cannot obtain device memory while
+ * they run: a worker sharing its GPU with a process that already holds the heap, a
+ * plug-in inside a framework whose pooling allocator owns it, or a latency path
+ * that cannot take the device-wide synchronisation an allocation implies.  The
+ * combiner's scratch (job counters + hash table, about 1 MiB) is a fixed array
+ * inside the library image; every GPU that loads liblocust.so holds it until the
+ * process exits.
+ *
+ * Limits (fixed, nothing grows): the input is at most LOCUST_STATIC_MAX_BYTES, it
+ * holds at most LOCUST_STATIC_MAX_KEYS distinct words, and no word is longer than
+ * 16 bytes.  A call beyond them fails with LOCUST_E_ARG (sizes passed in) or
+ * LOCUST_E_CAPACITY (found while counting) and says why in errbuf.
+ *
+ *   dev_data, nbytes   input text in device memory of the current device
+ *   dev_records        device buffer for max_records records of 32 bytes:
+ *                      {k0, k1, count, 0} as four little-endian uint64; k0/k1 are
+ *                      the word's bytes zero padded to 16.  Order is unspecified
+ *                      (these are combined partials, not the sorted result).
+ *   n_records          out: records written (on "dev_records is too small": needed)
+ *   stream             cudaStream_t to run on (NULL = default stream); the call
+ *                      returns after the work on it has finished
+ *   errbuf, errlen     optional buffer for an error message
+ *
+ * Runs on the calling thread's current device.  The first call on a device also
+ * does a one-time set-up (it resolves the address of the scratch array and sets a
+ * kernel attribute); make that first call before any stream capture begins.
+ * All calls on a device share the one scratch array: the table is cleared at the
+ * start of every call, and two calls whose GPU work overlaps (different streams or
+ * threads) race on it -- serialise them. */
+#define LOCUST_STATIC_MAX_KEYS   16384u
+#define LOCUST_STATIC_MAX_BYTES  (1ull << 32)
+int locust_count_static(const void *dev_data, uint64_t nbytes, void *dev_records, uint64_t max_records,
+                        uint64_t *n_records, void *stream, char *errbuf, size_t errlen);
+
 /* Library version string. */
 const char *locust_version(void);
 

@@ -24,8 +24,10 @@ EXPORTS = [
     "locust_process", "locust_reduce", "locust_wordcount", "locust_result_host",
     "locust_result_device", "locust_format_result", "locust_stage_ms", "locust_stats",
     "locust_last_error", "locust_shuffle_sizes", "locust_shuffle_pack",
-    "locust_shuffle_begin_merge", "locust_shuffle_merge",
+    "locust_shuffle_begin_merge", "locust_shuffle_merge", "locust_count_static",
 ]
+STATIC_MAX_KEYS = 16384
+STATIC_MAX_BYTES = 1 << 32
 
 
 class LocustError(RuntimeError):
@@ -75,8 +77,24 @@ def load():
     L.locust_shuffle_pack.argtypes = [vp, u32, vp, pp(u64)]
     L.locust_shuffle_begin_merge.argtypes = [vp]
     L.locust_shuffle_merge.argtypes = [vp, vp, u64]
+    L.locust_count_static.argtypes = [vp, u64, vp, u64, pp(u64), vp, ctypes.c_char_p, ctypes.c_size_t]
     _lib = L
     return L
+
+
+def count_static(dev_data_ptr, nbytes, dev_records_ptr, max_records, stream=None):
+    """locust_count_static: tokenise + combine without any allocation, for callers that cannot
+    obtain device memory (see include/locust.h).  Works on raw device addresses of the current
+    device; returns the number of 32-byte {k0, k1, count, 0} records written to dev_records."""
+    L = load()
+    n = ctypes.c_uint64()
+    err = ctypes.create_string_buffer(256)
+    rc = L.locust_count_static(dev_data_ptr, nbytes, dev_records_ptr, max_records, ctypes.byref(n), stream, err, 256)
+    if rc != 0:
+        e = LocustError("locust_count_static failed (%d): %s" % (rc, err.value.decode()))
+        e.code, e.needed = rc, n.value
+        raise e
+    return n.value
 
 
 def _ptr_of(data):
