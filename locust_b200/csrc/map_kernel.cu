@@ -5,25 +5,35 @@
 // (main.cu:415, :161-238): instead of emitting one 40-byte record per token and
 // sorting them all, every token is counted into a hash table keyed by its bytes.
 //
-// Layout.  One persistent CTA of 32 warps per SM.  A warp owns a contiguous range
-// of 512-byte rows; each lane holds 16 bytes of the row in registers (one
-// coalesced 128-bit load) and the next two rows are already in flight or
-// classified.  Word boundaries come from a SWAR delimiter classifier
-// (common.cuh) and neighbour-lane shuffles; token bytes are cut out of the
-// registers with PRMT, never re-read from memory.  Tokens of up to 8 bytes are
-// counted in a 16 K-slot shared-memory table (exact 64-bit keys), everything else
-// in the global table (exact 128-bit keys, 128-bit CAS).  Tokens longer than 16
-// bytes are listed by address for the process stage.
+// Layout.  One persistent CTA of 32 warps per SM; warps work on their own.  A warp
+// owns a contiguous range of 512-byte rows.  Per row:
+//   A. each lane holds 16 bytes (one coalesced 128-bit load, two rows prefetched in
+//      registers), classifies them with the SWAR delimiter classifier (common.cuh),
+//      stages bytes and delimiter bits in the warp's shared-memory area and writes
+//      the positions of its token starts into a dense list (warp prefix sum);
+//   B. the warp walks that list 32 tokens at a time, one token per lane, so every
+//      lane is busy whatever the token lengths: token length from the staged
+//      delimiter bits, token bytes from the staged row (PRMT), tokens of <= 8 bytes
+//      counted in a 2-way shared-memory table (exact 64-bit keys), misses and tokens
+//      of 9..16 bytes queued and inserted into the global table (exact 128-bit keys,
+//      128-bit CAS) 32 at a time; longer tokens are listed by address.
 #include "kernels.cuh"
 #include "../../include/locust.h"
 
 namespace locust {
 
-constexpr int kLogSmemSlots = 14;
-constexpr uint32_t kSmemSlots = 1u << kLogSmemSlots;
-constexpr uint32_t kQueueSlots = 64;             // per warp, 16 bytes each
 constexpr int kMapThreads = 1024;
-constexpr uint32_t kSmemBytes = kSmemSlots * (8 + 4) + (kMapThreads / 32) * kQueueSlots * 16;
+constexpr int kMapWarps = kMapThreads / 32;
+constexpr uint32_t kBuckets = 6656;               // shared table: buckets of two 64-bit keys
+constexpr uint32_t kSmemSlots = 2 * kBuckets;
+constexpr uint32_t kQueueSlots = 64;              // per warp, 16 bytes each
+// per-warp area: staged row (512 + 32), delimiter bits (17 words, padded), token list, queue
+constexpr uint32_t kRowOff = 0, kBitsOff = 544, kDescOff = 624, kQueueOff = 1136;
+constexpr uint32_t kWarpArea = kQueueOff + kQueueSlots * 16;           // 2160
+constexpr uint32_t kKeysBytes = kBuckets * 16, kCntBytes = kSmemSlots * 4;
+constexpr uint32_t kSmemBytes = kKeysBytes + kCntBytes + kMapWarps * kWarpArea;
+static_assert(kSmemBytes <= 232448, "shared memory budget of one CTA");
+static_assert(kWarpArea % 16 == 0 && kQueueOff % 16 == 0, "alignment");
 constexpr uint32_t kFull = 0xFFFFFFFFu;
 constexpr uint32_t kMaxProbe = 1u << 14;
 
@@ -66,28 +76,41 @@ __device__ __noinline__ void global_insert(const MapParams &p, uint64_t k0, uint
     atomicOr(&p.ctr->status, kStatusTableFull);
 }
 
-// Counts a token of <= 8 bytes in the CTA's shared table; false if both probed
-// slots belong to other keys.
-LC_D bool smem_insert(uint64_t *skeys, uint32_t *scnt, uint32_t lo, uint32_t hi) {
+// Per-warp view of shared memory.
+struct WarpCtx {
+    ulonglong2 *skeys;     // kBuckets buckets {key way 0, key way 1}
+    uint32_t *scnt;        // 2 * kBuckets counters
+    uint8_t *row;          // staged row + look-ahead
+    uint32_t *bits;        // delimiter bits of the row + look-ahead
+    uint16_t *desc;        // positions of token starts
+    ulonglong2 *queue;     // keys waiting for the global table
+    uint32_t qn;           // entries queued (warp-uniform)
+    uint32_t lane;
+    bool use_smem;
+};
+
+// Counts a token of <= 8 bytes (key = lo | hi << 32, never 0) in the CTA's table.
+// One 128-bit load reads both ways of the bucket.  False if the bucket is taken by
+// two other keys (or a claim was lost): the caller sends the key to the global table.
+LC_D bool smem_insert(const WarpCtx &wc, uint32_t lo, uint32_t hi) {
     const uint32_t h = lo * 0x9E3779B1u + hi * 0x85EBCA77u;
-    uint32_t slot = h >> (32 - kLogSmemSlots);
-    const uint64_t k = (uint64_t)lo | ((uint64_t)hi << 32);
-#pragma unroll
-    for (int probe = 0; probe < 2; ++probe) {
-        const uint64_t cur = skeys[slot];
-        if (cur == k) { atomicAdd(&scnt[slot], 1u); return true; }
-        if (cur == 0ull) {
-            const unsigned long long old = atomicCAS(reinterpret_cast<unsigned long long *>(&skeys[slot]), 0ull, k);
-            if (old == 0ull || old == k) { atomicAdd(&scnt[slot], 1u); return true; }
-        }
-        slot = (slot + 1) & (kSmemSlots - 1);
+    const uint32_t b = __umulhi(h, kBuckets);
+    const unsigned long long k = (unsigned long long)lo | ((unsigned long long)hi << 32);
+    const ulonglong2 kb = wc.skeys[b];
+    if (kb.x == k) { atomicAdd(&wc.scnt[2 * b], 1u); return true; }
+    if (kb.y == k) { atomicAdd(&wc.scnt[2 * b + 1], 1u); return true; }
+    if (kb.x == 0ull || kb.y == 0ull) {
+        const uint32_t way = kb.x == 0ull ? 0u : 1u;
+        unsigned long long *slot = reinterpret_cast<unsigned long long *>(wc.skeys) + 2 * b + way;
+        const unsigned long long old = atomicCAS(slot, 0ull, k);
+        if (old == 0ull || old == k) { atomicAdd(&wc.scnt[2 * b + way], 1u); return true; }
     }
     return false;
 }
 
-// Byte-serial path for one token starting at base[pos]: tokens that leave the
-// register window, second tokens of a word, rows with bytes >= 0x80.
-__device__ __noinline__ void token_generic(const MapParams &p, uint64_t *skeys, uint32_t *scnt, uint64_t pos) {
+// Byte-serial path for one token starting at base[pos]: tokens longer than 16 bytes
+// and the LOCUST_F_GENERIC_TOKENISER test switch.
+__device__ __noinline__ void token_generic(const MapParams &p, const WarpCtx &wc, uint64_t pos) {
     const uint8_t *s = p.base + pos;
     const uint64_t maxlen = p.hi - pos;
     uint64_t k0 = 0, k1 = 0, L = 0;
@@ -105,8 +128,8 @@ __device__ __noinline__ void token_generic(const MapParams &p, uint64_t *skeys, 
         else atomicOr(&p.ctr->status, kStatusLongFull);
         return;
     }
-    if (L <= 8 && !(p.flags & LOCUST_F_NO_SMEM_COMBINER)) {
-        if (smem_insert(skeys, scnt, (uint32_t)k0, (uint32_t)(k0 >> 32))) return;
+    if (L <= 8 && wc.use_smem) {
+        if (smem_insert(wc, (uint32_t)k0, (uint32_t)(k0 >> 32))) return;
     }
     global_insert(p, k0, k1, 1ull);
 }
@@ -131,19 +154,6 @@ LC_D uint4 load_chunk(const MapParams &p, uint64_t row, uint32_t lane) {
     return v;
 }
 
-// Per-warp state of the combiner: the CTA's shared table and this warp's queue of
-// keys that have to go to the global table.  Deferring them costs a few
-// instructions per step; inserting them one batch of 32 at a time keeps every lane
-// busy in the long global-insert code instead of one or two.
-struct WarpCtx {
-    uint64_t *skeys;
-    uint32_t *scnt;
-    ulonglong2 *queue;     // kQueueSlots entries, this warp's
-    uint32_t qn;           // entries queued (warp-uniform)
-    uint32_t lane;
-    bool use_smem;
-};
-
 LC_D void drain_queue(const MapParams &p, WarpCtx &wc, uint32_t keep_below) {
     // pops batches of up to 32 keys until fewer than keep_below remain
     while (wc.qn >= keep_below && wc.qn > 0u) {
@@ -158,19 +168,26 @@ LC_D void drain_queue(const MapParams &p, WarpCtx &wc, uint32_t keep_below) {
     }
 }
 
-// All lanes call this together.  `has` marks the lanes that hold a token of L <= 16
-// bytes whose bytes start at byte `o` of w0.  Short tokens are counted in the shared
-// table; misses and tokens of 9..16 bytes are queued for the global table.
+// Phase B for one batch: lane `wc.lane` takes token number t of the row (if active).
+// All lanes call this together.
 template <bool ASCII>
-LC_D void handle_token(const MapParams &p, WarpCtx &wc, bool has, uint32_t o, uint32_t L, uint32_t w0, uint32_t w1,
-                       uint32_t w2, uint32_t w3, uint32_t w4) {
-    uint32_t a = 0, b = 0, c = 0, d = 0;
-    bool defer = false;
-    if (has) {
-        if (ASCII) extract_key16_ascii(w0, w1, w2, w3, w4, o, L, a, b, c, d);
-        else extract_key16_any(w0, w1, w2, w3, w4, o, L, a, b, c, d);
-        defer = !(L <= 8u && wc.use_smem && smem_insert(wc.skeys, wc.scnt, a, b));
-    }
+LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool active, uint32_t t, uint64_t row_pos) {
+    const uint32_t *row32 = reinterpret_cast<const uint32_t *>(wc.row);
+    const uint32_t pos = active ? wc.desc[t] : 0u;
+    // token length: first delimiter at or after pos, within 17 bits
+    const uint32_t wi = pos >> 5;
+    const uint32_t win = __funnelshift_r(wc.bits[wi], wc.bits[wi + 1], pos & 31u) & 0x1FFFFu;
+    const uint32_t L = (uint32_t)__ffs((int)win) - 1u;            // win == 0 -> 0xFFFFFFFF
+    const bool has = active && win != 0u;
+    const bool far = active && win == 0u;
+    // token bytes: five aligned words starting at the word that holds pos
+    const uint32_t bi = pos >> 2, o = pos & 3u;
+    const uint32_t w0 = row32[bi], w1 = row32[bi + 1], w2 = row32[bi + 2], w3 = row32[bi + 3], w4 = row32[bi + 4];
+    uint32_t a, b, c, d;
+    if (ASCII) extract_key16_ascii(w0, w1, w2, w3, w4, o, L, a, b, c, d);
+    else extract_key16_any(w0, w1, w2, w3, w4, o, L, a, b, c, d);
+    bool defer = has;
+    if (has && L <= 8u && wc.use_smem) defer = !smem_insert(wc, a, b);
     const uint32_t m = __ballot_sync(kFull, defer);
     if (m) {
         if (defer)
@@ -179,62 +196,38 @@ LC_D void handle_token(const MapParams &p, WarpCtx &wc, bool has, uint32_t o, ui
         wc.qn += __popc(m);
         if (wc.qn >= 32u) drain_queue(p, wc, 32u);
     }
-}
-
-template <bool ASCII>
-LC_D void tokenise_row(const MapParams &p, WarpCtx &wc, const uint32_t (&w)[8], uint32_t starts, uint32_t dd,
-                       uint64_t chunk_pos) {
-    uint32_t rem = starts;
-    // first token of each 4-byte word: register indices are static
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const uint32_t sj = (starts >> (4 * j)) & 0xFu;
-        const uint32_t o = low_bit4(sj);
-        const uint32_t pp = 4 * j + o;
-        const uint32_t L = (uint32_t)__ffs((int)(dd >> pp)) - 1u;            // no delimiter in the window -> huge
-        const bool has = sj != 0u && L <= 16u;
-        if (has) rem &= ~(1u << pp);
-        handle_token<ASCII>(p, wc, has, o, L, w[j], w[j + 1], w[j + 2], w[j + 3], w[j + 4]);
-    }
-    // what is left: second tokens of a word (dynamic word index) and tokens that leave the window
-    while (__any_sync(kFull, rem != 0u)) {
-        const uint32_t pp = rem ? (uint32_t)__ffs((int)rem) - 1u : 0u;
-        const uint32_t L = (uint32_t)__ffs((int)(dd >> pp)) - 1u;
-        const bool has = rem != 0u && L <= 16u;
-        const bool far = rem != 0u && L > 16u;
-        rem &= rem - 1u;
-        const uint32_t j = pp >> 2;
-        const uint32_t t0 = (j & 1u) ? w[1] : w[0], t1 = (j & 1u) ? w[2] : w[1], t2 = (j & 1u) ? w[3] : w[2],
-                       t3 = (j & 1u) ? w[4] : w[3], t4 = (j & 1u) ? w[5] : w[4], t5 = (j & 1u) ? w[6] : w[5],
-                       t6 = (j & 1u) ? w[7] : w[6];
-        const uint32_t v0 = (j & 2u) ? t2 : t0, v1 = (j & 2u) ? t3 : t1, v2 = (j & 2u) ? t4 : t2,
-                       v3 = (j & 2u) ? t5 : t3, v4 = (j & 2u) ? t6 : t4;
-        handle_token<ASCII>(p, wc, has, pp & 3u, L, v0, v1, v2, v3, v4);
-        if (far) token_generic(p, wc.skeys, wc.scnt, chunk_pos + pp);
+    if (__any_sync(kFull, far)) {
+        if (far) token_generic(p, wc, row_pos + pos);
         __syncwarp();
     }
 }
 
 __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const __grid_constant__ MapParams p) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
-    uint64_t *skeys = reinterpret_cast<uint64_t *>(smem_raw);
-    uint32_t *scnt = reinterpret_cast<uint32_t *>(smem_raw + kSmemSlots * 8);
-    for (uint32_t i = threadIdx.x; i < kSmemSlots; i += kMapThreads) { skeys[i] = 0ull; scnt[i] = 0u; }
+    {
+        uint4 *z = reinterpret_cast<uint4 *>(smem_raw);
+        for (uint32_t i = threadIdx.x; i < (kKeysBytes + kCntBytes) / 16; i += kMapThreads) z[i] = make_uint4(0, 0, 0, 0);
+    }
     __syncthreads();
 
-    const uint32_t lane = threadIdx.x & 31u;
-    const uint64_t nwarps = (uint64_t)gridDim.x * (kMapThreads / 32);
-    const uint64_t gw = (uint64_t)blockIdx.x * (kMapThreads / 32) + (threadIdx.x >> 5);
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint64_t nwarps = (uint64_t)gridDim.x * kMapWarps;
+    const uint64_t gw = (uint64_t)blockIdx.x * kMapWarps + warp;
     const uint64_t nrows = (p.hi + 511ull) >> 9;
     const uint64_t r0 = nrows * gw / nwarps, r1 = nrows * (gw + 1) / nwarps;
     const bool use_fast = !(p.flags & LOCUST_F_GENERIC_TOKENISER);
     WarpCtx wc;
-    wc.skeys = skeys;
-    wc.scnt = scnt;
-    wc.queue = reinterpret_cast<ulonglong2 *>(smem_raw + kSmemSlots * 12) + (threadIdx.x >> 5) * kQueueSlots;
+    wc.skeys = reinterpret_cast<ulonglong2 *>(smem_raw);
+    wc.scnt = reinterpret_cast<uint32_t *>(smem_raw + kKeysBytes);
+    uint8_t *area = smem_raw + kKeysBytes + kCntBytes + warp * kWarpArea;
+    wc.row = area + kRowOff;
+    wc.bits = reinterpret_cast<uint32_t *>(area + kBitsOff);
+    wc.desc = reinterpret_cast<uint16_t *>(area + kDescOff);
+    wc.queue = reinterpret_cast<ulonglong2 *>(area + kQueueOff);
     wc.qn = 0u;
     wc.lane = lane;
     wc.use_smem = !(p.flags & LOCUST_F_NO_SMEM_COMBINER);
+    uint16_t *bits16 = reinterpret_cast<uint16_t *>(wc.bits);
 
     if (r0 < r1) {
         uint4 c = load_chunk(p, r0, lane);
@@ -251,27 +244,42 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
         }
         for (uint64_t row = r0; row < r1; ++row) {
             const uint4 nn = load_chunk(p, row + 2, lane);                 // in flight while this row is tokenised
-            const uint32_t d_up = __shfl_sync(kFull, lane == 0 ? dn : dc, (lane + 1) & 31);
             const uint32_t d_dn = __shfl_sync(kFull, lane == 31 ? pd : dc, (lane + 31) & 31);
-            const uint32_t starts = ~dc & ((dc << 1) | (d_dn >> 15)) & 0xFFFFu;
-            const uint32_t dd = dc | (d_up << 16);
-            const uint64_t chunk_pos = row * 512ull + lane * 16u;
+            uint32_t starts = ~dc & ((dc << 1) | (d_dn >> 15)) & 0xFFFFu;
+            const uint64_t row_pos = row * 512ull;
             if (use_fast) {
-                // 32-byte window: this lane's chunk and the next lane's (lane 31: next row's first chunk)
-                uint32_t w[8];
-                w[0] = c.x; w[1] = c.y; w[2] = c.z; w[3] = c.w;
-                w[4] = __shfl_sync(kFull, lane == 0 ? n.x : c.x, (lane + 1) & 31);
-                w[5] = __shfl_sync(kFull, lane == 0 ? n.y : c.y, (lane + 1) & 31);
-                w[6] = __shfl_sync(kFull, lane == 0 ? n.z : c.z, (lane + 1) & 31);
-                w[7] = __shfl_sync(kFull, lane == 0 ? n.w : c.w, (lane + 1) & 31);
-                if (asc_c && asc_n) tokenise_row<true>(p, wc, w, starts, dd, chunk_pos);
-                else tokenise_row<false>(p, wc, w, starts, dd, chunk_pos);
+                // A: stage bytes and delimiter bits (with the next row's first chunks as look-ahead)
+                reinterpret_cast<uint4 *>(wc.row)[lane] = c;
+                if (lane < 2) reinterpret_cast<uint4 *>(wc.row)[32 + lane] = n;
+                bits16[lane] = (uint16_t)dc;
+                if (lane < 4) bits16[32 + lane] = (uint16_t)dn;
+                // dense list of token starts: warp prefix sum of the per-lane counts
+                const uint32_t cnt = __popc(starts);
+                uint32_t incl = cnt;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t y = __shfl_up_sync(kFull, incl, o);
+                    if (lane >= (uint32_t)o) incl += y;
+                }
+                const uint32_t total = __shfl_sync(kFull, incl, 31);
+                uint32_t at = incl - cnt;
+                while (starts) {
+                    wc.desc[at++] = (uint16_t)(lane * 16u + (uint32_t)__ffs((int)starts) - 1u);
+                    starts &= starts - 1u;
+                }
+                __syncwarp();
+                // B: one token per lane, 32 at a time
+                if (asc_c && asc_n) {
+                    for (uint32_t t0 = 0; t0 < total; t0 += 32) process_batch<true>(p, wc, t0 + lane < total, t0 + lane, row_pos);
+                } else {
+                    for (uint32_t t0 = 0; t0 < total; t0 += 32) process_batch<false>(p, wc, t0 + lane < total, t0 + lane, row_pos);
+                }
+                __syncwarp();
             } else {
-                uint32_t rem = starts;
-                while (rem) {
-                    const uint32_t pp = (uint32_t)__ffs((int)rem) - 1u;
-                    rem &= rem - 1u;
-                    token_generic(p, skeys, scnt, chunk_pos + pp);
+                while (starts) {
+                    const uint32_t pp = (uint32_t)__ffs((int)starts) - 1u;
+                    starts &= starts - 1u;
+                    token_generic(p, wc, row_pos + lane * 16u + pp);
                 }
                 __syncwarp();
             }
@@ -284,9 +292,10 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
     }
     __syncthreads();
     // flush the CTA's combiner into the global table
+    const unsigned long long *keys = reinterpret_cast<const unsigned long long *>(wc.skeys);
     for (uint32_t i = threadIdx.x; i < kSmemSlots; i += kMapThreads) {
-        const uint64_t k = skeys[i];
-        if (k) global_insert(p, k, 0ull, (unsigned long long)scnt[i]);
+        const unsigned long long k = keys[i];
+        if (k) global_insert(p, k, 0ull, (unsigned long long)wc.scnt[i]);
     }
 }
 
@@ -297,10 +306,9 @@ cudaError_t map_kernel_setup() {
 int launch_tokenize_combine(const MapParams &p, int num_sms, cudaStream_t st) {
     if (p.hi <= p.lo) return 0;
     const uint64_t nrows = (p.hi + 511ull) >> 9;
-    uint64_t ctas = (nrows + (kMapThreads / 32) - 1) / (kMapThreads / 32);
+    uint64_t ctas = (nrows + kMapWarps - 1) / kMapWarps;
     if (ctas > (uint64_t)num_sms) ctas = (uint64_t)num_sms;
     tokenize_combine_kernel<<<(unsigned)ctas, kMapThreads, kSmemBytes, st>>>(p);
     return 1;
 }
-
 }  // namespace locust
