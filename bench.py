@@ -168,8 +168,8 @@ def main():
     table_log2 = args.table_log2 or (17 if name == "C2" else 22)
     wc = locust_b200.WordCount(device=local_rank, table_log2=table_log2, stream=stream.cuda_stream)
     if world > 1:
-        from locust_b200.shuffle import DistributedWordCount
-        job = DistributedWordCount(wc, dist, dev, stream)
+        from locust_b200.shuffle import DistributedWordCount, GpuBackend
+        job = DistributedWordCount(GpuBackend(wc, dev), dist)
         step = lambda buf: job.run(buf)
     else:
         step = lambda buf: wc.run(buf)

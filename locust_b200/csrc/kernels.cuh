@@ -22,6 +22,15 @@ struct LongTok {
     uint64_t len;
 };
 
+// One entry of the long-token list: `count` occurrences of the key at ptr[0..len).
+// MAP writes one entry per occurrence (count 1); merged shuffle records carry sums.
+struct LongOcc {
+    const uint8_t *ptr;
+    uint64_t len;
+    unsigned long long count;
+    uint64_t pad;
+};
+
 // Device-side scalars of one job.
 struct Counters {
     unsigned long long n_long;      // long-token occurrences seen (can exceed the buffer)
@@ -41,7 +50,7 @@ struct MapParams {
     uint64_t lo, hi;
     Slot *table;
     uint64_t table_mask;        // slots - 1
-    LongTok *long_list;
+    LongOcc *long_list;
     uint64_t long_cap;
     Counters *ctr;
     uint32_t flags;             // LOCUST_F_*
@@ -84,7 +93,7 @@ int launch_tokenize_combine(const MapParams &p, int num_sms, cudaStream_t st);
 
 // PROCESS
 int launch_extract(const Slot *table, uint64_t slots, Records r, Counters *ctr, int num_sms, cudaStream_t st);
-int launch_append_long(const LongTok *list, uint64_t long_cap, Records r, Counters *ctr, int num_sms, cudaStream_t st);
+int launch_append_long(const LongOcc *list, uint64_t long_cap, Records r, Counters *ctr, int num_sms, cudaStream_t st);
 // epoch: first of 16 consecutive look-back epochs this sort may use
 int launch_sort_records(Records r, SortScratch s, Counters *ctr, uint32_t epoch, int num_sms, cudaStream_t st);
 int launch_tie_fix(Records r, Counters *ctr, int num_sms, cudaStream_t st);
@@ -106,12 +115,19 @@ int launch_exclusive_scan_u64(const unsigned long long *in, unsigned long long *
                               uint64_t n_max, uint64_t *lb_state, uint32_t *ticket, uint32_t epoch,
                               unsigned long long *total, bool append_total, int num_sms, cudaStream_t st);
 
-// SHUFFLE (multi-GPU): records of 32 bytes {k0, k1, count, 0}
-int launch_shuffle_count(const Slot *table, uint64_t slots, uint32_t nparts, unsigned long long *part_counts,
-                         int num_sms, cudaStream_t st);
-int launch_shuffle_pack(const Slot *table, uint64_t slots, uint32_t nparts, uint8_t *out,
-                        const unsigned long long *part_offsets, unsigned long long *part_cursors, int num_sms,
+// SHUFFLE (multi-GPU)
+// Part layout: 32-byte header {n_short, long_bytes, 0, 0}, n_short records of 32 bytes
+// {k0, k1, count, 0}, then long records {len, count, key bytes padded to 16}.
+// part_counts: 2 * nparts scalars (short records, long bytes per part).
+int launch_shuffle_count(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
+                         const Counters *ctr, uint32_t nparts, unsigned long long *part_counts, int num_sms,
+                         cudaStream_t st);
+// part_offsets: nparts byte offsets into out; part_cursors: 2 * nparts scalars, zeroed by the caller
+int launch_shuffle_pack(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
+                        const Counters *ctr, uint32_t nparts, uint8_t *out, const unsigned long long *part_offsets,
+                        const unsigned long long *part_counts, unsigned long long *part_cursors, int num_sms,
                         cudaStream_t st);
-int launch_shuffle_merge(const uint8_t *records, uint64_t nrec, MapParams p, int num_sms, cudaStream_t st);
+// adds one received part to the table / long list of p
+int launch_shuffle_merge(const uint8_t *part, uint64_t nbytes, MapParams p, int num_sms, cudaStream_t st);
 
 }  // namespace locust

@@ -35,7 +35,7 @@ struct locust_ctx {
 
     Slot *table = nullptr;
     uint64_t slots = 0;
-    LongTok *long_list = nullptr;
+    LongOcc *long_list = nullptr;
     uint64_t long_cap = 0;
     Counters *ctr = nullptr;        // device
     Counters *h_ctr = nullptr;      // pinned host mirror
@@ -58,8 +58,10 @@ struct locust_ctx {
     unsigned long long *line_off = nullptr;  uint64_t line_cap = 0;
     char *d_text = nullptr;  uint64_t d_text_cap = 0;
     char *h_text = nullptr;  uint64_t h_text_cap = 0;
-    // shuffle scratch
-    unsigned long long *part_counts = nullptr;  uint32_t part_cap = 0;
+    // shuffle scratch: device [counts 2n | cursors 2n | offsets n], host copies of counts and offsets
+    unsigned long long *part_dev = nullptr;  uint32_t part_cap = 0;
+    std::vector<unsigned long long> part_host, part_off_host;
+    uint32_t part_n = 0;
 
     cudaEvent_t ev[6]{};            // map, process, reduce: begin/end
     bool ev_set[6]{};
@@ -231,6 +233,45 @@ int run_reduce_async(locust_ctx *c) {
     return LOCUST_OK;
 }
 
+// Grows whatever the status bits name and runs MAP again over the recorded inputs.
+int grow_and_remap(locust_ctx *c, uint32_t st) {
+    if (c->shuffled) return fail(c, LOCUST_E_CAPACITY, "table too small for the merged partials; raise table_log2 / long_capacity");
+    int rc;
+    if (st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull)) {
+        uint64_t slots = c->slots, long_cap = c->long_cap;
+        if (st & kStatusTableFull) slots *= 4;
+        if (st & kStatusLongFull) { long_cap = c->h_ctr->n_long + (c->h_ctr->n_long >> 3) + 1024; }
+        if ((st & kStatusEntryFull) && !(st & (kStatusTableFull | kStatusLongFull))) slots *= 2;
+        if (slots > (1ull << 32)) return fail(c, LOCUST_E_CAPACITY, "combiner table would exceed 2^32 slots");
+        rc = alloc_sized(c, slots, long_cap);
+        if (rc) return rc;
+    } else {   // only the key blob was too small
+        cudaFree(c->red.key_blob); c->red.key_blob = nullptr;
+        c->red.blob_cap = c->h_ctr->blob_bytes + 64;
+        CU(dalloc(&c->red.key_blob, c->red.blob_cap));
+    }
+    rc = clear_job(c);
+    if (rc) return rc;
+    CU(cudaEventRecord(c->ev[0], c->stream));
+    for (const auto &s : c->segments) { rc = run_map_segment(c, s); if (rc) return rc; }
+    CU(cudaEventRecord(c->ev[1], c->stream));
+    return LOCUST_OK;
+}
+
+// After MAP, before the partials leave the device: waits for the kernels and makes sure
+// no buffer overflowed (growing and redoing MAP if one did).
+int ensure_map_ok(locust_ctx *c) {
+    for (int attempt = 0; attempt < 8; ++attempt) {
+        CU(cudaMemcpyAsync(c->h_ctr, c->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        const uint32_t st = c->h_ctr->status;
+        if (!(st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull))) return LOCUST_OK;
+        int rc = grow_and_remap(c, st);
+        if (rc) return rc;
+    }
+    return fail(c, LOCUST_E_CAPACITY, "buffers still too small after repeated growth");
+}
+
 // Runs REDUCE, reads the counters back and, if a fixed-size buffer was too small,
 // grows it and redoes the job from the recorded input segments.
 int finish_reduce(locust_ctx *c) {
@@ -243,26 +284,17 @@ int finish_reduce(locust_ctx *c) {
             c->stage = 2;
             return LOCUST_OK;
         }
-        if (c->shuffled) return fail(c, LOCUST_E_CAPACITY, "table too small for merged partials; raise table_log2");
-        if (st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull)) {
-            uint64_t slots = c->slots, long_cap = c->long_cap;
-            if (st & kStatusTableFull) slots *= 4;
-            if (st & kStatusLongFull) { long_cap = c->h_ctr->n_long + (c->h_ctr->n_long >> 3) + 1024; }
-            if ((st & kStatusEntryFull) && !(st & (kStatusTableFull | kStatusLongFull))) slots *= 2;
-            if (slots > (1ull << 32)) return fail(c, LOCUST_E_CAPACITY, "combiner table would exceed 2^32 slots");
-            rc = alloc_sized(c, slots, long_cap);
-            if (rc) return rc;
-        } else {   // only the key blob was too small
+        if (c->shuffled && (st & kStatusBlobFull) && !(st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull))) {
+            // merged records stay in the table: only the blob has to grow, then PROCESS + REDUCE again
             cudaFree(c->red.key_blob); c->red.key_blob = nullptr;
             c->red.blob_cap = c->h_ctr->blob_bytes + 64;
             CU(dalloc(&c->red.key_blob, c->red.blob_cap));
+            CU(cudaMemsetAsync(&c->ctr->n_entries, 0, sizeof(unsigned long long), c->stream));
+            CU(cudaMemsetAsync(&c->ctr->status, 0, sizeof(uint32_t), c->stream));
+        } else {
+            rc = grow_and_remap(c, st);
+            if (rc) return rc;
         }
-        // redo from the inputs
-        rc = clear_job(c);
-        if (rc) return rc;
-        CU(cudaEventRecord(c->ev[0], c->stream));
-        for (const auto &s : c->segments) { rc = run_map_segment(c, s); if (rc) return rc; }
-        CU(cudaEventRecord(c->ev[1], c->stream));
         rc = run_process(c);
         if (rc) return rc;
     }
@@ -350,7 +382,7 @@ int locust_destroy(locust_ctx *c) {
     cudaFree(c->table); cudaFree(c->long_list); cudaFree(c->ctr);
     free_record_buffers(c);
     cudaFree(c->sort.hist); cudaFree(c->sort.bases); cudaFree(c->sort.tickets);
-    cudaFree(c->line_off); cudaFree(c->d_text); cudaFree(c->part_counts);
+    cudaFree(c->line_off); cudaFree(c->d_text); cudaFree(c->part_dev);
     cudaFreeHost(c->h_ctr); cudaFreeHost(c->h_blob); cudaFreeHost(c->h_offsets);
     cudaFreeHost(c->h_counts); cudaFreeHost(c->h_vals); cudaFreeHost(c->h_text);
     for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
@@ -518,21 +550,81 @@ int locust_stats(locust_ctx *c, uint64_t *tokens, uint64_t *unique_keys, uint64_
 const char *locust_last_error(locust_ctx *c) { return c ? c->err.c_str() : "null context"; }
 
 // ---- multi-GPU shuffle ------------------------------------------------------------------
+static uint64_t part_bytes(uint64_t n_short, uint64_t long_bytes) {
+    return (32ull + 32ull * n_short + long_bytes + 31ull) & ~31ull;
+}
+
 int locust_shuffle_sizes(locust_ctx *c, uint32_t nparts, uint64_t *bytes_per_part) {
     if (!c || !bytes_per_part || nparts == 0) return LOCUST_E_ARG;
-    return fail(c, LOCUST_E_STATE, "shuffle not built yet");
+    if (c->stage != 0) return fail(c, LOCUST_E_STATE, "locust_shuffle_sizes after locust_process");
+    CU(cudaSetDevice(c->device));
+    if (!c->cleared) {            // nothing mapped on this rank: an empty job still takes part in the exchange
+        CU(cudaEventRecord(c->ev[0], c->stream)); c->ev_set[0] = true;
+        int rc0 = clear_job(c);
+        if (rc0) return rc0;
+        CU(cudaEventRecord(c->ev[1], c->stream)); c->ev_set[1] = true;
+    }
+    int rc = ensure_map_ok(c);
+    if (rc) return rc;
+    if (nparts > c->part_cap) {
+        cudaFree(c->part_dev); c->part_dev = nullptr;
+        c->part_cap = nparts;
+        CU(dalloc(&c->part_dev, 5ull * nparts));
+    }
+    c->part_n = nparts;
+    c->part_host.assign(2ull * nparts, 0ull);
+    CU(cudaMemsetAsync(c->part_dev, 0, 4ull * nparts * sizeof(unsigned long long), c->stream));
+    c->launches += (uint64_t)launch_shuffle_count(c->table, c->slots, c->long_list, c->long_cap, c->ctr, nparts,
+                                                  c->part_dev, c->num_sms, c->stream);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(c->part_host.data(), c->part_dev, 2ull * nparts * sizeof(unsigned long long),
+                       cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    for (uint32_t i = 0; i < nparts; ++i) bytes_per_part[i] = part_bytes(c->part_host[i], c->part_host[nparts + i]);
+    return LOCUST_OK;
 }
+
 int locust_shuffle_pack(locust_ctx *c, uint32_t nparts, void *dev_out, const uint64_t *part_offsets) {
     if (!c || !dev_out || !part_offsets || nparts == 0) return LOCUST_E_ARG;
-    return fail(c, LOCUST_E_STATE, "shuffle not built yet");
+    if (c->stage != 0 || c->part_n != nparts) return fail(c, LOCUST_E_STATE, "locust_shuffle_pack needs locust_shuffle_sizes with the same nparts first");
+    CU(cudaSetDevice(c->device));
+    c->part_off_host.assign(part_offsets, part_offsets + nparts);
+    for (uint32_t i = 0; i < nparts; ++i)
+        if (part_offsets[i] % 32) return fail(c, LOCUST_E_ARG, "part offsets must be multiples of 32");
+    CU(cudaMemcpyAsync(c->part_dev + 4ull * nparts, c->part_off_host.data(), nparts * sizeof(unsigned long long),
+                       cudaMemcpyHostToDevice, c->stream));
+    c->launches += (uint64_t)launch_shuffle_pack(c->table, c->slots, c->long_list, c->long_cap, c->ctr, nparts,
+                                                 static_cast<uint8_t *>(dev_out), c->part_dev + 4ull * nparts, c->part_dev,
+                                                 c->part_dev + 2ull * nparts, c->num_sms, c->stream);
+    CU(cudaGetLastError());
+    // the host vector is read by the async copy: wait for it before the caller can call us again
+    CU(cudaStreamSynchronize(c->stream));
+    return LOCUST_OK;
 }
+
 int locust_shuffle_begin_merge(locust_ctx *c) {
     if (!c) return LOCUST_E_ARG;
-    return fail(c, LOCUST_E_STATE, "shuffle not built yet");
+    if (c->stage != 0) return fail(c, LOCUST_E_STATE, "locust_shuffle_begin_merge after locust_process");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemsetAsync(c->table, 0, c->slots * sizeof(Slot), c->stream));
+    CU(cudaMemsetAsync(c->ctr, 0, sizeof(Counters), c->stream));
+    c->cleared = true;
+    c->shuffled = true;
+    c->part_n = 0;
+    return LOCUST_OK;
 }
+
 int locust_shuffle_merge(locust_ctx *c, const void *dev_records, uint64_t nbytes) {
     if (!c || (!dev_records && nbytes)) return LOCUST_E_ARG;
-    return fail(c, LOCUST_E_STATE, "shuffle not built yet");
+    if (c->stage != 0 || !c->shuffled) return fail(c, LOCUST_E_STATE, "locust_shuffle_merge needs locust_shuffle_begin_merge first");
+    if (nbytes == 0) return LOCUST_OK;
+    if (nbytes < 32 || nbytes % 32) return fail(c, LOCUST_E_ARG, "a packed part is a multiple of 32 bytes");
+    CU(cudaSetDevice(c->device));
+    MapParams p = map_params(c, static_cast<const uint8_t *>(dev_records), 0, 0);
+    c->launches += (uint64_t)launch_shuffle_merge(static_cast<const uint8_t *>(dev_records), nbytes, p, c->num_sms, c->stream);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(c->ev[1], c->stream)); c->ev_set[1] = true;
+    return LOCUST_OK;
 }
 
 }  // extern "C"

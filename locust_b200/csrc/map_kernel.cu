@@ -124,7 +124,7 @@ __device__ __noinline__ void token_generic(const MapParams &p, const WarpCtx &wc
         L = 17;
         while (L < maxlen && !is_delim(s[L])) ++L;
         const unsigned long long idx = atomicAdd(&p.ctr->n_long, 1ull);
-        if (idx < p.long_cap) { p.long_list[idx].ptr = s; p.long_list[idx].len = L; }
+        if (idx < p.long_cap) { p.long_list[idx].ptr = s; p.long_list[idx].len = L; p.long_list[idx].count = 1ull; }
         else atomicOr(&p.ctr->status, kStatusLongFull);
         return;
     }
@@ -213,8 +213,9 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint64_t nwarps = (uint64_t)gridDim.x * kMapWarps;
     const uint64_t gw = (uint64_t)blockIdx.x * kMapWarps + warp;
-    const uint64_t nrows = (p.hi + 511ull) >> 9;
-    const uint64_t r0 = nrows * gw / nwarps, r1 = nrows * (gw + 1) / nwarps;
+    // rows of 512 bytes counted from base; only rows that overlap [lo, hi) are handed out
+    const uint64_t row_lo = p.lo >> 9, nrows = ((p.hi + 511ull) >> 9) - row_lo;
+    const uint64_t r0 = row_lo + nrows * gw / nwarps, r1 = row_lo + nrows * (gw + 1) / nwarps;
     const bool use_fast = !(p.flags & LOCUST_F_GENERIC_TOKENISER);
     WarpCtx wc;
     wc.skeys = reinterpret_cast<ulonglong2 *>(smem_raw);
@@ -299,13 +300,61 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
     }
 }
 
+// ---- merge side of the shuffle (loadIntermediateFile's role, main.cu:66-103) ---------
+// One received part: header {n_short, long_bytes}, short records {k0, k1, count, 0},
+// long records {len, count, bytes padded to 16}.  Short records go through the same
+// table insert as MAP; long records are appended to the long-token list, pointing
+// into the received buffer.
+__global__ void __launch_bounds__(256) shuffle_merge_kernel(const uint8_t *__restrict__ part, uint64_t nbytes,
+                                                            const __grid_constant__ MapParams p) {
+    const unsigned long long *hdr = reinterpret_cast<const unsigned long long *>(part);
+    const unsigned long long n_short = hdr[0], long_bytes = hdr[1];
+    if (32ull + 32ull * n_short + long_bytes > nbytes) {            // malformed part: refuse loudly
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(&p.ctr->status, kStatusEntryFull);
+        return;
+    }
+    const ulonglong4 *rec = reinterpret_cast<const ulonglong4 *>(part + 32);
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_short;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const ulonglong4 v = rec[i];
+        global_insert(p, v.x, v.y, v.z);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {                      // long records are rare: one thread walks them
+        const uint8_t *q = part + 32ull + 32ull * n_short;
+        unsigned long long done = 0;
+        while (done < long_bytes) {
+            const unsigned long long len = reinterpret_cast<const unsigned long long *>(q + done)[0];
+            const unsigned long long cnt = reinterpret_cast<const unsigned long long *>(q + done)[1];
+            const unsigned long long idx = atomicAdd(&p.ctr->n_long, 1ull);
+            if (idx < p.long_cap) {
+                p.long_list[idx].ptr = q + done + 16;
+                p.long_list[idx].len = len;
+                p.long_list[idx].count = cnt;
+            } else {
+                atomicOr(&p.ctr->status, kStatusLongFull);
+            }
+            done += 16ull + ((len + 15ull) & ~15ull);
+        }
+    }
+}
+
+int launch_shuffle_merge(const uint8_t *part, uint64_t nbytes, MapParams p, int num_sms, cudaStream_t st) {
+    if (nbytes < 32) return 0;
+    uint64_t g = (nbytes / 32 + 255) / 256;
+    const uint64_t cap = (uint64_t)num_sms * 8;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    shuffle_merge_kernel<<<(unsigned)g, 256, 0, st>>>(part, nbytes, p);
+    return 1;
+}
+
 cudaError_t map_kernel_setup() {
     return cudaFuncSetAttribute(tokenize_combine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
 }
 
 int launch_tokenize_combine(const MapParams &p, int num_sms, cudaStream_t st) {
     if (p.hi <= p.lo) return 0;
-    const uint64_t nrows = (p.hi + 511ull) >> 9;
+    const uint64_t nrows = ((p.hi + 511ull) >> 9) - (p.lo >> 9);
     uint64_t ctas = (nrows + kMapWarps - 1) / kMapWarps;
     if (ctas > (uint64_t)num_sms) ctas = (uint64_t)num_sms;
     tokenize_combine_kernel<<<(unsigned)ctas, kMapThreads, kSmemBytes, st>>>(p);

@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(256) extract_kernel(const Slot *__restrict__ t
 }
 
 // every occurrence of a long token becomes a record with count 1; REDUCE merges them
-__global__ void __launch_bounds__(256) append_long_kernel(const LongTok *__restrict__ list, uint64_t long_cap,
+__global__ void __launch_bounds__(256) append_long_kernel(const LongOcc *__restrict__ list, uint64_t long_cap,
                                                           Records r, Counters *ctr) {
     unsigned long long n = ctr->n_long;
     if (n > long_cap) n = long_cap;
@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(256) append_long_kernel(const LongTok *__restr
          i += (unsigned long long)gridDim.x * blockDim.x) {
         const unsigned long long e = base + i;
         if (e >= r.cap) { atomicOr(&ctr->status, kStatusEntryFull); continue; }
-        const LongTok t = list[i];
+        const LongOcc t = list[i];
         uint64_t b0 = 0, b1 = 0;
 #pragma unroll
         for (int b = 0; b < 8; ++b) {
@@ -73,8 +73,9 @@ __global__ void __launch_bounds__(256) append_long_kernel(const LongTok *__restr
             b1 = (b1 << 8) | t.ptr[8 + b];
         }
         r.a0[e] = b0; r.a1[e] = b1; r.ia[e] = (uint32_t)e;
-        r.count[e] = 1ull;
-        r.ref[e] = t;
+        r.count[e] = t.count;
+        r.ref[e].ptr = t.ptr;
+        r.ref[e].len = t.len;
     }
 }
 __global__ void bump_entries_kernel(uint64_t long_cap, uint64_t cap, Counters *ctr) {
@@ -272,7 +273,7 @@ int launch_extract(const Slot *table, uint64_t slots, Records r, Counters *ctr, 
     return 1;
 }
 
-int launch_append_long(const LongTok *list, uint64_t long_cap, Records r, Counters *ctr, int num_sms,
+int launch_append_long(const LongOcc *list, uint64_t long_cap, Records r, Counters *ctr, int num_sms,
                        cudaStream_t st) {
     append_long_kernel<<<grid_for(long_cap, 256, num_sms, 4), 256, 0, st>>>(list, long_cap, r, ctr);
     bump_entries_kernel<<<1, 1, 0, st>>>(long_cap, r.cap, ctr);

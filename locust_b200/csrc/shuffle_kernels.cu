@@ -1,0 +1,99 @@
+// shuffle_kernels.cu -- packing of a device's partial (word, count) records into one
+// part per destination, destination = hash(word) % nparts.
+//
+// Stands in for writeKeyIntValues -> /tmp/out.txt (MapReduce/src/main.cu:116-124,
+// :428-430): the reference hands partials to the reduce stage through a text file,
+// here they are packed in device memory for an all-to-all over NVLink.  The merge
+// side (loadIntermediateFile, main.cu:66-103) is shuffle_merge_kernel in
+// map_kernel.cu, next to the table insert it shares with MAP.
+#include "kernels.cuh"
+
+namespace locust {
+
+LC_D uint32_t part_of_short(uint64_t k0, uint64_t k1, uint32_t nparts) {
+    return (uint32_t)(hash_key128(k0, k1) >> 32) % nparts;
+}
+LC_D uint32_t part_of_long(const uint8_t *ptr, uint64_t len, uint32_t nparts) {
+    uint64_t h = 1469598103934665603ull;
+    for (uint64_t i = 0; i < len; ++i) { h ^= ptr[i]; h *= 1099511628211ull; }
+    return (uint32_t)(mix64(h) >> 32) % nparts;
+}
+LC_D uint64_t long_record_bytes(uint64_t len) { return 16ull + ((len + 15ull) & ~15ull); }
+
+__global__ void __launch_bounds__(256) shuffle_count_kernel(const Slot *__restrict__ table, uint64_t slots,
+                                                            const LongOcc *__restrict__ long_list, uint64_t long_cap,
+                                                            const Counters *ctr, uint32_t nparts,
+                                                            unsigned long long *part_counts) {
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < slots; i += stride) {
+        const ulonglong2 k = *reinterpret_cast<const ulonglong2 *>(table + i);
+        if ((k.x | k.y) != 0ull) atomicAdd(&part_counts[part_of_short(k.x, k.y, nparts)], 1ull);
+    }
+    unsigned long long nl = ctr->n_long;
+    if (nl > long_cap) nl = long_cap;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nl; i += stride) {
+        const LongOcc t = long_list[i];
+        atomicAdd(&part_counts[nparts + part_of_long(t.ptr, t.len, nparts)], long_record_bytes(t.len));
+    }
+}
+
+__global__ void __launch_bounds__(256) shuffle_pack_kernel(const Slot *__restrict__ table, uint64_t slots,
+                                                           const LongOcc *__restrict__ long_list, uint64_t long_cap,
+                                                           const Counters *ctr, uint32_t nparts, uint8_t *out,
+                                                           const unsigned long long *__restrict__ part_offsets,
+                                                           const unsigned long long *__restrict__ part_counts,
+                                                           unsigned long long *part_cursors) {
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid < nparts) {       // headers
+        unsigned long long *h = reinterpret_cast<unsigned long long *>(out + part_offsets[tid]);
+        h[0] = part_counts[tid]; h[1] = part_counts[nparts + tid]; h[2] = 0ull; h[3] = 0ull;
+    }
+    for (uint64_t i = tid; i < slots; i += stride) {
+        const ulonglong4 v = *reinterpret_cast<const ulonglong4 *>(table + i);
+        if ((v.x | v.y) == 0ull) continue;
+        const uint32_t part = part_of_short(v.x, v.y, nparts);
+        const unsigned long long at = atomicAdd(&part_cursors[part], 1ull);
+        ulonglong4 *dst = reinterpret_cast<ulonglong4 *>(out + part_offsets[part] + 32ull) + at;
+        *dst = make_ulonglong4(v.x, v.y, v.z, 0ull);
+    }
+    unsigned long long nl = ctr->n_long;
+    if (nl > long_cap) nl = long_cap;
+    for (uint64_t i = tid; i < nl; i += stride) {
+        const LongOcc t = long_list[i];
+        const uint32_t part = part_of_long(t.ptr, t.len, nparts);
+        const unsigned long long at = atomicAdd(&part_cursors[nparts + part], long_record_bytes(t.len));
+        uint8_t *dst = out + part_offsets[part] + 32ull + 32ull * part_counts[part] + at;
+        reinterpret_cast<unsigned long long *>(dst)[0] = t.len;
+        reinterpret_cast<unsigned long long *>(dst)[1] = t.count;
+        const uint64_t padded = (t.len + 15ull) & ~15ull;
+        for (uint64_t b = 0; b < padded; ++b) dst[16 + b] = b < t.len ? t.ptr[b] : (uint8_t)0;
+    }
+}
+
+static inline unsigned grid_for(uint64_t n, int num_sms) {
+    uint64_t g = (n + 1023) / 1024;
+    const uint64_t cap = (uint64_t)num_sms * 8;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (unsigned)g;
+}
+
+int launch_shuffle_count(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
+                         const Counters *ctr, uint32_t nparts, unsigned long long *part_counts, int num_sms,
+                         cudaStream_t st) {
+    shuffle_count_kernel<<<grid_for(slots, num_sms), 256, 0, st>>>(table, slots, long_list, long_cap, ctr, nparts,
+                                                                  part_counts);
+    return 1;
+}
+
+int launch_shuffle_pack(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
+                        const Counters *ctr, uint32_t nparts, uint8_t *out, const unsigned long long *part_offsets,
+                        const unsigned long long *part_counts, unsigned long long *part_cursors, int num_sms,
+                        cudaStream_t st) {
+    shuffle_pack_kernel<<<grid_for(slots, num_sms), 256, 0, st>>>(table, slots, long_list, long_cap, ctr, nparts, out,
+                                                                 part_offsets, part_counts, part_cursors);
+    return 1;
+}
+
+}  // namespace locust

@@ -1,0 +1,131 @@
+"""Multi-GPU word count: one process per GPU, shards by byte range, partial (word, count)
+records exchanged by hash(word) % P.
+
+Replaces the reference's multi mode -- `[line_start, line_end)` windows per node
+(MapReduce/src/main.cu:367-374), sorted partials written to /tmp/out.txt (:428-430), a TCP
+command channel (Distributor/slave.py) -- with an all-to-all over NVLink:
+
+    map (each rank, its shard)            locust_map
+    pack partials by destination          locust_shuffle_sizes / locust_shuffle_pack
+    all-to-all of sizes, then of records  torch.distributed (NCCL; gloo in the CPU tests)
+    merge what arrived                    locust_shuffle_begin_merge / locust_shuffle_merge
+    gather the partitions on rank 0       the same pack / exchange / merge with one destination
+    process + reduce on rank 0            locust_process / locust_reduce  -> sorted result
+
+torch.distributed is plumbing only; every byte of arithmetic happens in liblocust.so.  The class
+is written against a small backend interface so the exchange logic can be tested on CPU with
+gloo (tests/test_shuffle_host.py) without a GPU.
+"""
+
+DELIMS = b" ,.-;:'()\"\t\n"
+
+
+def plan_shards(data, nparts):
+    """Byte ranges [(lo, hi)] of `data` (bytes-like) for nparts ranks: nominal r*N/P, moved
+    forward to the first position whose preceding byte is a delimiter, so no token straddles
+    two ranks.  Works on any delimiter, not only newlines."""
+    n = len(data)
+    cuts = [0]
+    for r in range(1, nparts):
+        c = max(cuts[-1], (r * n) // nparts)
+        while 0 < c < n and data[c - 1] not in DELIMS:
+            c += 1
+        cuts.append(min(c, n))
+    cuts.append(n)
+    return [(cuts[i], cuts[i + 1]) for i in range(nparts)]
+
+
+class GpuBackend:
+    """liblocust.so + torch CUDA tensors."""
+
+    def __init__(self, wc, device):
+        import torch
+        self.wc, self.device, self.torch = wc, device, torch
+
+    def alloc(self, nbytes):
+        return self.torch.empty(max(int(nbytes), 32), dtype=self.torch.uint8, device=self.device)
+
+    def sizes_tensor(self, values):
+        return self.torch.tensor(values, dtype=self.torch.int64, device=self.device)
+
+    def reset(self):
+        self.wc.reset()
+
+    def map(self, buf):
+        self.wc.map(buf)
+
+    def shuffle_sizes(self, nparts):
+        return self.wc.shuffle_sizes(nparts)
+
+    def shuffle_pack(self, nparts, out, offsets):
+        self.wc.shuffle_pack(nparts, out.data_ptr(), offsets)
+
+    def begin_merge(self):
+        self.wc.shuffle_begin_merge()
+
+    def merge(self, buf, offset, nbytes):
+        self.wc.shuffle_merge(buf.data_ptr() + offset, nbytes, keepalive=buf)
+
+    def process(self):
+        self.wc.process()
+
+    def reduce(self):
+        self.wc.reduce()
+
+
+class DistributedWordCount:
+    """run(shard) on every rank; afterwards rank 0's backend holds the sorted result of the
+    whole input and the other ranks hold an empty one."""
+
+    def __init__(self, backend, dist, group=None):
+        self.b, self.dist, self.group = backend, dist, group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.last_shuffle_bytes = 0          # bytes this rank sent to other ranks in the hash shuffle
+
+    def _exchange(self, send_sizes):
+        """all-to-all of per-destination byte counts; returns what each source sends to me"""
+        t_send = self.b.sizes_tensor(send_sizes)
+        t_recv = self.b.sizes_tensor([0] * self.world)
+        self.dist.all_to_all_single(t_recv, t_send, group=self.group)
+        return [int(x) for x in t_recv.tolist()]
+
+    def _shuffle(self, nparts_local, dest_of_part):
+        """pack the local records into nparts_local parts, send part i to rank dest_of_part[i],
+        merge everything received"""
+        b = self.b
+        sizes = b.shuffle_sizes(nparts_local)
+        send_sizes = [0] * self.world
+        for i, s in enumerate(sizes):
+            send_sizes[dest_of_part[i]] += s
+        offsets, acc = [], 0
+        for s in sizes:
+            offsets.append(acc)
+            acc += s
+        sendbuf = b.alloc(acc)
+        b.shuffle_pack(nparts_local, sendbuf, offsets)
+        recv_sizes = self._exchange(send_sizes)
+        recvbuf = b.alloc(sum(recv_sizes))
+        self.dist.all_to_all_single(recvbuf[:sum(recv_sizes)], sendbuf[:acc], output_split_sizes=recv_sizes,
+                                    input_split_sizes=send_sizes, group=self.group)
+        b.begin_merge()
+        off = 0
+        for s in recv_sizes:
+            if s:
+                b.merge(recvbuf, off, s)
+            off += s
+        return send_sizes
+
+    def run(self, shard):
+        b = self.b
+        b.reset()
+        b.map(shard)
+        if self.world > 1:
+            # hash-partitioned exchange: part i goes to rank i
+            sent = self._shuffle(self.world, list(range(self.world)))
+            self.last_shuffle_bytes = sum(s for r, s in enumerate(sent) if r != self.rank)
+            # gather: every rank's merged partition goes to rank 0 as one part
+            self._shuffle(1, [0])
+        b.process()
+        b.reduce()
+        return self

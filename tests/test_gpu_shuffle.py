@@ -1,0 +1,136 @@
+"""The CUDA side of the multi-GPU shuffle (locust_shuffle_* through the C ABI) on ONE GPU:
+P ranks are emulated by P contexts on cuda:0 and the all-to-all is done by handing each
+packed part to its destination context.  The exchange logic itself (torch.distributed) is
+covered on CPU in tests/test_shuffle_host.py and on real GPUs by bench.py --gpus N."""
+import random
+
+import pytest
+
+from conftest import golden_input
+from locust_b200.shuffle import plan_shards
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def lb():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import locust_b200
+    locust_b200.load()
+    return locust_b200
+
+
+def emulate(lb, data, P, **kw):
+    """word count of `data` over P emulated ranks; returns (keys, counts) of rank 0 and the
+    per-rank partition sizes after the hash shuffle"""
+    dev = torch.frombuffer(bytearray(data) if data else bytearray(1), dtype=torch.uint8)[:len(data)].cuda()
+    shards = plan_shards(data, P)
+    ctx = [lb.WordCount(device=0, **kw) for _ in range(P)]
+    keep = []
+
+    def exchange(nparts, dest_of_part, senders):
+        # pack on every sender, then deliver part i of sender s to context dest_of_part[i]
+        inbox = [[] for _ in range(P)]
+        for s in senders:
+            sizes = ctx[s].shuffle_sizes(nparts)
+            assert all(x % 32 == 0 and x >= 32 for x in sizes)
+            offs, acc = [], 0
+            for x in sizes:
+                offs.append(acc)
+                acc += x
+            buf = torch.zeros(acc, dtype=torch.uint8, device="cuda")
+            ctx[s].shuffle_pack(nparts, buf.data_ptr(), offs)
+            keep.append(buf)
+            for i, (o, x) in enumerate(zip(offs, sizes)):
+                inbox[dest_of_part[i]].append((buf, o, x))
+        for r in range(P):
+            ctx[r].shuffle_begin_merge()
+            for buf, o, x in inbox[r]:
+                ctx[r].shuffle_merge(buf.data_ptr() + o, x, keepalive=buf)
+
+    try:
+        for r, (lo, hi) in enumerate(shards):
+            ctx[r].reset()
+            ctx[r].map(dev[lo:hi])
+        exchange(P, list(range(P)), range(P))
+        # partition sizes: every key lives on exactly one rank now
+        exchange(1, [0], range(P))
+        sizes = []
+        for r in range(P):
+            ctx[r].process()
+            ctx[r].reduce()
+            sizes.append(ctx[r].stats()["unique_keys"])
+        keys, counts, _ = ctx[0].result()
+        return keys, counts, sizes
+    finally:
+        for c in ctx:
+            c.close()
+
+
+@pytest.mark.parametrize("P", [1, 2, 3, 8])
+def test_emulated_ranks_match_the_oracle(lb, P):
+    from oracle import pyoracle
+    data = golden_input("hamlet") + golden_input("edge_long_tokens") + b" " + golden_input("rand_longtok_s5")
+    keys, counts, sizes = emulate(lb, data, P, table_log2=14)
+    ref = pyoracle.wordcount(data)
+    assert keys == ref.keys and counts == ref.counts
+    assert sizes[0] == len(ref.keys) and all(s == 0 for s in sizes[1:])
+
+
+def test_hash_partitions_are_disjoint_and_balanced(lb):
+    from oracle import pyoracle
+    rng = random.Random(1)
+    words = [bytes(rng.choice(b"abcdefghij") for _ in range(rng.randint(1, 20))) for _ in range(30000)]
+    data = b" ".join(rng.choice(words) for _ in range(200000))
+    P = 4
+    dev = torch.frombuffer(bytearray(data), dtype=torch.uint8).cuda()
+    wc = lb.WordCount(device=0, table_log2=16)
+    wc.reset()
+    wc.map(dev)
+    sizes = wc.shuffle_sizes(P)
+    buf = torch.zeros(sum(sizes), dtype=torch.uint8, device="cuda")
+    offs = [sum(sizes[:i]) for i in range(P)]
+    wc.shuffle_pack(P, buf.data_ptr(), offs)
+    torch.cuda.synchronize()
+    raw = bytes(buf.cpu().numpy())
+    import struct
+    seen, total = {}, 0
+    for p_, (o, x) in enumerate(zip(offs, sizes)):
+        n_short, long_bytes, _, _ = struct.unpack_from("<4Q", raw, o)
+        assert (32 + 32 * n_short + long_bytes + 31) // 32 * 32 == x
+        q = o + 32
+        for _ in range(n_short):
+            k = raw[q:q + 16].rstrip(b"\0")
+            c = struct.unpack_from("<Q", raw, q + 16)[0]
+            assert k not in seen
+            seen[k] = (p_, c)
+            q += 32
+        end = q + long_bytes
+        while q < end:
+            ln, c = struct.unpack_from("<2Q", raw, q)
+            k = raw[q + 16:q + 16 + ln]
+            seen[k] = (p_, seen.get(k, (p_, 0))[1] + c)      # long keys: one record per occurrence
+            q += 16 + (ln + 15) // 16 * 16
+        total += n_short
+    ref = pyoracle.wordcount(data).as_dict()
+    assert {k: c for k, (_, c) in seen.items()} == ref
+    per_part = [sum(1 for _, (p_, _) in seen.items() if p_ == i) for i in range(P)]
+    assert min(per_part) > 0.8 * len(seen) / P                   # hash partitions are balanced
+    wc.close()
+
+
+def test_synthetic_c3_style_two_ranks(lb):
+    from oracle import pyoracle
+    from locust_b200.textgen import TextGen
+    n = 32 << 20
+    g = TextGen.config("C3", total_bytes=n, device=0, vocab=200000)
+    d = torch.empty(n, dtype=torch.uint8, device="cuda")
+    g.fill_device(d)
+    torch.cuda.synchronize()
+    host = bytes(d.cpu().numpy())
+    keys, counts, _ = emulate(lb, host, 2, table_log2=19)
+    ref = pyoracle.wordcount(host, mode="fast", formats=False)
+    assert keys == ref.keys and counts == ref.counts
