@@ -50,27 +50,37 @@ class ClockSampler(threading.Thread):
     def run(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             for line in self.proc.stdout:
                 self.rows.append([x.strip() for x in line.split(",")])
         except Exception:
             pass
 
-    def stop(self):
+    def wait_first_sample(self, timeout=3.0):
+        t0 = time.time()
+        while not self.rows and time.time() - t0 < timeout:
+            time.sleep(0.01)
+
+    def mark(self):
+        return len(self.rows)
+
+    def stop(self, lo=0, hi=None):
         if self.proc:
             self.proc.terminate()
         self.join(timeout=2)
-        sm = sorted(int(r[1]) for r in self.rows if len(r) > 8 and r[1].isdigit())
-        mx = [int(r[2]) for r in self.rows if len(r) > 8 and r[2].isdigit()]
+        window = self.rows[lo:hi] if len(self.rows[lo:hi]) >= 1 else self.rows
+        scope = "timed region" if window is not self.rows else "whole run (timed region shorter than one sample)"
+        sm = sorted(int(r[1]) for r in window if len(r) > 8 and r[1].isdigit())
+        mx = [int(r[2]) for r in window if len(r) > 8 and r[2].isdigit()]
         reasons = set()
-        for r in self.rows:
+        for r in window:
             if len(r) > 8:
                 for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
                     if v.lower().startswith("active"):
                         reasons.add(name)
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(self.rows)}
+                "reasons": sorted(reasons), "samples": len(window), "scope": scope}
 
 
 def workload(n_gpus):
@@ -182,7 +192,7 @@ def main():
 
     def timed(buf, k):
         """device time of k steps (ms, max over ranks) and the per-step map-kernel times"""
-        map_ms = []
+        map_ms, shuf = [], []
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         with torch.cuda.stream(stream):
@@ -190,6 +200,8 @@ def main():
             for _ in range(k):
                 step(buf)
                 map_ms.append(wc.stage_ms()[0])
+                if world > 1:
+                    shuf.append((wc.shuffle_ms(), job.last_shuffle_bytes))
             e1.record(stream)
         barrier()
         ms = e0.elapsed_time(e1)
@@ -197,16 +209,18 @@ def main():
             t = torch.tensor([ms], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
-        return ms, map_ms
+        return ms, map_ms, shuf
 
     # ---- device-resident input ("value") ----------------------------------------------
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    sampler.wait_first_sample()
     with torch.cuda.stream(stream):
         for _ in range(args.warmup):
             step(text)
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    ms, map_ms = timed(text, args.steps)
-    clocks = sampler.stop()
+    m0 = sampler.mark()
+    ms, map_ms, shuf = timed(text, args.steps)
+    m1 = sampler.mark()
     st = wc.stats()
     launches_per_step = st["kernel_launches"]
     uniq, tokens = st["unique_keys"], st["tokens"]
@@ -230,6 +244,15 @@ def main():
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "avg_kernel_ms": avg_map_ms,
                 "map_share_of_step": avg_map_ms * args.steps / ms}
+
+    shuffle = None
+    if world > 1 and shuf:
+        # both exchanges (hash shuffle + gather) with their host-side size round trips; bytes = what this
+        # rank sent to other ranks in the hash shuffle.  770 GB/s = measured peer copy per direction
+        # (B200_PROFILING.md); the shuffle here is latency-, not bandwidth-bound.
+        sms_, sb_ = sum(x for x, _ in shuf) / len(shuf), sum(b for _, b in shuf) / len(shuf)
+        shuffle = {"ms": sms_, "bytes_sent_rank0": sb_, "achieved_gbs": sb_ / (sms_ * 1e-3) / GB if sms_ > 0 else None,
+                   "peak_gbs": 770.0, "frac": (sb_ / (sms_ * 1e-3) / GB / 770.0) if sms_ > 0 else None}
 
     # ---- end to end: pinned host input in, host result out, every step ---------------------
     host = torch.empty(per_gpu, dtype=torch.uint8, pin_memory=True)
@@ -259,6 +282,8 @@ def main():
            "d2h_bytes_per_step": d2h, "steps": e2e_steps,
            "note": "locust_map(LOCUST_HOST) from pinned memory, chunked copy overlapped with map; result copied to host"}
 
+    clocks = sampler.stop(m0, m1)
+
     # ---- the reference's CPU algorithm on this box's host cores (rank 0, N=1) -----------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -276,7 +301,7 @@ def main():
                 "config": {"workload": desc, "bytes_per_gpu": per_gpu, "tokens_per_gpu": tokens if world == 1 else None,
                            "unique_keys": uniq, "table_log2": table_log2,
                            "l2": "input per step (%d MiB per GPU) is larger than the 126 MB L2" % (per_gpu >> 20)},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
+                "roofline": roofline, "shuffle": shuffle, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
                 "gpu_launches": launches_per_step * args.steps, "gpu_launches_per_step": launches_per_step,
                 "stage_ms_last_step": dict(zip(("map", "process", "reduce"), wc.stage_ms()))}
         print(json.dumps(line), flush=True)

@@ -45,6 +45,7 @@ extern "C" {
 #define LOCUST_STAGE_MAP      0
 #define LOCUST_STAGE_PROCESS  1
 #define LOCUST_STAGE_REDUCE   2
+#define LOCUST_STAGE_SHUFFLE  3   /* multi-GPU only: first locust_shuffle_sizes .. last locust_shuffle_merge */
 
 /* config flags */
 #define LOCUST_F_GENERIC_TOKENISER  1u  /* test switch: byte-serial token path for every token */

@@ -223,6 +223,10 @@ class WordCount:
     def stage_ms(self):
         return tuple(float(self._L.locust_stage_ms(self._h, s)) for s in (0, 1, 2))
 
+    def shuffle_ms(self):
+        """device time from the first shuffle_sizes to the last shuffle_merge of the job (-1 if none)"""
+        return float(self._L.locust_stage_ms(self._h, 3))
+
     def stats(self):
         u64 = ctypes.c_uint64
         t, u, k = u64(), u64(), u64()

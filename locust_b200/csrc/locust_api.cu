@@ -63,8 +63,8 @@ struct locust_ctx {
     std::vector<unsigned long long> part_host, part_off_host;
     uint32_t part_n = 0;
 
-    cudaEvent_t ev[6]{};            // map, process, reduce: begin/end
-    bool ev_set[6]{};
+    cudaEvent_t ev[8]{};            // map, process, reduce, shuffle: begin/end
+    bool ev_set[8]{};
     uint64_t launches = 0;
     std::string err;
 };
@@ -530,7 +530,7 @@ int locust_format_result(locust_ctx *c, int cpu_format, const char **text, uint6
 }
 
 float locust_stage_ms(locust_ctx *c, int stage) {
-    if (!c || stage < 0 || stage > 2) return -1.0f;
+    if (!c || stage < 0 || stage > 3) return -1.0f;
     if (!c->ev_set[2 * stage] || !c->ev_set[2 * stage + 1]) return -1.0f;
     cudaSetDevice(c->device);
     if (cudaEventSynchronize(c->ev[2 * stage + 1]) != cudaSuccess) return -1.0f;
@@ -566,6 +566,7 @@ int locust_shuffle_sizes(locust_ctx *c, uint32_t nparts, uint64_t *bytes_per_par
     }
     int rc = ensure_map_ok(c);
     if (rc) return rc;
+    if (!c->ev_set[6]) { CU(cudaEventRecord(c->ev[6], c->stream)); c->ev_set[6] = true; }
     if (nparts > c->part_cap) {
         cudaFree(c->part_dev); c->part_dev = nullptr;
         c->part_cap = nparts;
@@ -623,7 +624,7 @@ int locust_shuffle_merge(locust_ctx *c, const void *dev_records, uint64_t nbytes
     MapParams p = map_params(c, static_cast<const uint8_t *>(dev_records), 0, 0);
     c->launches += (uint64_t)launch_shuffle_merge(static_cast<const uint8_t *>(dev_records), nbytes, p, c->num_sms, c->stream);
     CU(cudaGetLastError());
-    CU(cudaEventRecord(c->ev[1], c->stream)); c->ev_set[1] = true;
+    CU(cudaEventRecord(c->ev[7], c->stream)); c->ev_set[7] = true;
     return LOCUST_OK;
 }
 

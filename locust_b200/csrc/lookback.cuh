@@ -26,19 +26,32 @@ LC_D uint64_t lb_load(const uint64_t *p) {
 }
 
 // Sum of the values of tiles [0, tile) in column `col` of a status array laid out
-// as state[tile * stride + col]; stops at the first inclusive word.
+// as state[tile * stride + col]; stops at the first inclusive word.  The words of up
+// to eight predecessors are requested at once, so the walk costs about one memory
+// round trip per eight tiles instead of one per tile.
 LC_D uint64_t lb_lookback(const uint64_t *state, uint32_t tile, uint32_t stride, uint32_t col, uint32_t epoch) {
     uint64_t sum = 0;
-    for (uint32_t t = tile; t-- > 0;) {
-        uint64_t w;
-        uint32_t spins = 0;
-        for (;;) {
-            w = lb_load(state + (uint64_t)t * stride + col);
-            if ((uint32_t)(w >> 56) == epoch && ((w >> 54) & 3ull) != 0ull) break;
-            if (++spins > 16) __nanosleep(64);
+    uint32_t t = tile;
+    while (t > 0) {
+        const uint32_t batch = t < 8u ? t : 8u;
+        uint64_t w[8];
+#pragma unroll
+        for (uint32_t i = 0; i < 8; ++i)
+            if (i < batch) w[i] = lb_load(state + (uint64_t)(t - 1u - i) * stride + col);
+#pragma unroll
+        for (uint32_t i = 0; i < 8; ++i) {
+            if (i < batch) {
+                uint64_t x = w[i];
+                uint32_t spins = 0;
+                while ((uint32_t)(x >> 56) != epoch || ((x >> 54) & 3ull) == 0ull) {
+                    if (++spins > 16) __nanosleep(64);
+                    x = lb_load(state + (uint64_t)(t - 1u - i) * stride + col);
+                }
+                sum += x & kLbValueMask;
+                if (((x >> 54) & 3ull) == kLbInclusive) return sum;
+            }
         }
-        sum += w & kLbValueMask;
-        if (((w >> 54) & 3ull) == kLbInclusive) break;
+        t -= batch;
     }
     return sum;
 }

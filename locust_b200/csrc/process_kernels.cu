@@ -109,31 +109,32 @@ __global__ void __launch_bounds__(256) sort_hist_kernel(Records r, const Counter
 
 // one block: per digit position, bucket bases and whether the pass moves anything
 __global__ void __launch_bounds__(256) sort_prep_kernel(const uint32_t *hist, uint32_t *bases, Counters *ctr) {
-    __shared__ uint32_t warp_tot[8];
-    __shared__ uint32_t uniform;
+    __shared__ uint32_t warp_tot[2][8];
     const uint32_t d = threadIdx.x, lane = d & 31u, w = d >> 5;
     const unsigned long long n = ctr->n_entries;
     uint32_t parity = 0;
+    uint32_t hv[16];
+#pragma unroll
+    for (int p = 0; p < 16; ++p) hv[p] = hist[p * 256 + d];        // all loads in flight together
+#pragma unroll
     for (int p = 0; p < 16; ++p) {
-        if (d == 0) uniform = 0u;
-        __syncthreads();
-        const uint32_t v = hist[p * 256 + d];
-        if ((unsigned long long)v == n) uniform = 1u;       // every key has this digit (also n == 0)
+        const uint32_t v = hv[p];
+        // every key has the same digit here (also n == 0): the pass would move nothing
+        const uint32_t uniform = __syncthreads_or((unsigned long long)v == n);
         uint32_t x = v;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t y = __shfl_up_sync(kFull, x, o);
             if (lane >= (uint32_t)o) x += y;
         }
-        if (lane == 31) warp_tot[w] = x;
+        if (lane == 31) warp_tot[p & 1][w] = x;
         __syncthreads();
         uint32_t off = 0;
-        for (uint32_t k = 0; k < w; ++k) off += warp_tot[k];
+        for (uint32_t k = 0; k < w; ++k) off += warp_tot[p & 1][k];
         bases[p * 256 + d] = off + x - v;
         const uint32_t active = uniform ? 0u : 1u;
         if (d == 0) { ctr->pass_active[p] = active; ctr->pass_src[p] = parity; }
         parity ^= active;
-        __syncthreads();
     }
     if (d == 0) ctr->sort_parity = parity;
 }
