@@ -24,7 +24,7 @@ namespace locust {
 
 constexpr int kMapThreads = 1024;
 constexpr int kMapWarps = kMapThreads / 32;
-constexpr uint32_t kBuckets = 6656;               // shared table: buckets of two 64-bit keys
+constexpr uint32_t kBuckets = (232448u - (kMapThreads / 32) * 2160u) / 24u / 8u * 8u;               // shared table: buckets of two 64-bit keys
 constexpr uint32_t kSmemSlots = 2 * kBuckets;
 constexpr uint32_t kQueueSlots = 64;              // per warp, 16 bytes each
 // per-warp area: staged row (512 + 32), delimiter bits (17 words, padded), token list, queue
@@ -134,22 +134,25 @@ __device__ __noinline__ void token_generic(const MapParams &p, const WarpCtx &wc
     global_insert(p, k0, k1, 1ull);
 }
 
+// Chunk at byte offset `off` that straddles lo or hi: bytes outside [lo, hi) read as '\n'.
+__device__ __noinline__ uint4 mask_chunk(const MapParams &p, uint64_t off, uint4 v) {
+    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int b = 0; b < 16; ++b) {
+        const uint64_t q = off + b;
+        if (q < p.lo || q >= p.hi)
+            w[b >> 2] = (w[b >> 2] & ~(0xFFu << (8 * (b & 3)))) | (0x0Au << (8 * (b & 3)));
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
 // 16 bytes of row `row` for this lane; bytes outside [lo, hi) read as '\n'.
 LC_D uint4 load_chunk(const MapParams &p, uint64_t row, uint32_t lane) {
     const uint64_t off = row * 512ull + lane * 16u;
     uint4 v = make_uint4(0x0A0A0A0Au, 0x0A0A0A0Au, 0x0A0A0A0Au, 0x0A0A0A0Au);
     if (off < p.hi) {
         v = ldg_stream(p.base + off);
-        if (off < p.lo || off + 16 > p.hi) {
-            uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-            for (int b = 0; b < 16; ++b) {
-                const uint64_t q = off + b;
-                if (q < p.lo || q >= p.hi)
-                    w[b >> 2] = (w[b >> 2] & ~(0xFFu << (8 * (b & 3)))) | (0x0Au << (8 * (b & 3)));
-            }
-            v = make_uint4(w[0], w[1], w[2], w[3]);
-        }
+        if (off < p.lo || off + 16 > p.hi) v = mask_chunk(p, off, v);
     }
     return v;
 }
@@ -170,8 +173,7 @@ LC_D void drain_queue(const MapParams &p, WarpCtx &wc, uint32_t keep_below) {
 
 // Phase B for one batch: lane `wc.lane` takes token number t of the row (if active).
 // All lanes call this together.
-template <bool ASCII>
-LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool active, uint32_t t, uint64_t row_pos) {
+LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active, uint32_t t, uint64_t row_pos) {
     const uint32_t *row32 = reinterpret_cast<const uint32_t *>(wc.row);
     const uint32_t pos = active ? wc.desc[t] : 0u;
     // token length: first delimiter at or after pos, within 17 bits
@@ -184,7 +186,7 @@ LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool active, uint32_t t
     const uint32_t bi = pos >> 2, o = pos & 3u;
     const uint32_t w0 = row32[bi], w1 = row32[bi + 1], w2 = row32[bi + 2], w3 = row32[bi + 3], w4 = row32[bi + 4];
     uint32_t a, b, c, d;
-    if (ASCII) extract_key16_ascii(w0, w1, w2, w3, w4, o, L, a, b, c, d);
+    if (ascii) extract_key16_ascii(w0, w1, w2, w3, w4, o, L, a, b, c, d);      // warp-uniform branch
     else extract_key16_any(w0, w1, w2, w3, w4, o, L, a, b, c, d);
     bool defer = has;
     if (has && L <= 8u && wc.use_smem) defer = !smem_insert(wc, a, b);
@@ -270,11 +272,9 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
                 }
                 __syncwarp();
                 // B: one token per lane, 32 at a time
-                if (asc_c && asc_n) {
-                    for (uint32_t t0 = 0; t0 < total; t0 += 32) process_batch<true>(p, wc, t0 + lane < total, t0 + lane, row_pos);
-                } else {
-                    for (uint32_t t0 = 0; t0 < total; t0 += 32) process_batch<false>(p, wc, t0 + lane < total, t0 + lane, row_pos);
-                }
+                const bool ascii = asc_c && asc_n;
+#pragma unroll 1
+                for (uint32_t t0 = 0; t0 < total; t0 += 32) process_batch(p, wc, ascii, t0 + lane < total, t0 + lane, row_pos);
                 __syncwarp();
             } else {
                 while (starts) {
