@@ -258,20 +258,6 @@ int grow_and_remap(locust_ctx *c, uint32_t st) {
     return LOCUST_OK;
 }
 
-// After MAP, before the partials leave the device: waits for the kernels and makes sure
-// no buffer overflowed (growing and redoing MAP if one did).
-int ensure_map_ok(locust_ctx *c) {
-    for (int attempt = 0; attempt < 8; ++attempt) {
-        CU(cudaMemcpyAsync(c->h_ctr, c->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
-        CU(cudaStreamSynchronize(c->stream));
-        const uint32_t st = c->h_ctr->status;
-        if (!(st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull))) return LOCUST_OK;
-        int rc = grow_and_remap(c, st);
-        if (rc) return rc;
-    }
-    return fail(c, LOCUST_E_CAPACITY, "buffers still too small after repeated growth");
-}
-
 // Runs REDUCE, reads the counters back and, if a fixed-size buffer was too small,
 // grows it and redoes the job from the recorded input segments.
 int finish_reduce(locust_ctx *c) {
@@ -564,8 +550,6 @@ int locust_shuffle_sizes(locust_ctx *c, uint32_t nparts, uint64_t *bytes_per_par
         if (rc0) return rc0;
         CU(cudaEventRecord(c->ev[1], c->stream)); c->ev_set[1] = true;
     }
-    int rc = ensure_map_ok(c);
-    if (rc) return rc;
     if (!c->ev_set[6]) { CU(cudaEventRecord(c->ev[6], c->stream)); c->ev_set[6] = true; }
     if (nparts > c->part_cap) {
         cudaFree(c->part_dev); c->part_dev = nullptr;
@@ -574,13 +558,23 @@ int locust_shuffle_sizes(locust_ctx *c, uint32_t nparts, uint64_t *bytes_per_par
     }
     c->part_n = nparts;
     c->part_host.assign(2ull * nparts, 0ull);
-    CU(cudaMemsetAsync(c->part_dev, 0, 4ull * nparts * sizeof(unsigned long long), c->stream));
-    c->launches += (uint64_t)launch_shuffle_count(c->table, c->slots, c->long_list, c->long_cap, c->ctr, nparts,
-                                                  c->part_dev, c->num_sms, c->stream);
-    CU(cudaGetLastError());
-    CU(cudaMemcpyAsync(c->part_host.data(), c->part_dev, 2ull * nparts * sizeof(unsigned long long),
-                       cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
+    // count optimistically and read the job counters back in the same round trip; if MAP
+    // overflowed a buffer, grow, redo MAP and count again
+    for (int attempt = 0;; ++attempt) {
+        CU(cudaMemsetAsync(c->part_dev, 0, 4ull * nparts * sizeof(unsigned long long), c->stream));
+        c->launches += (uint64_t)launch_shuffle_count(c->table, c->slots, c->long_list, c->long_cap, c->ctr, nparts,
+                                                      c->part_dev, c->num_sms, c->stream);
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(c->part_host.data(), c->part_dev, 2ull * nparts * sizeof(unsigned long long),
+                           cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(c->h_ctr, c->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        const uint32_t st = c->h_ctr->status;
+        if (!(st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull))) break;
+        if (attempt >= 8) return fail(c, LOCUST_E_CAPACITY, "buffers still too small after repeated growth");
+        int rc = grow_and_remap(c, st);
+        if (rc) return rc;
+    }
     for (uint32_t i = 0; i < nparts; ++i) bytes_per_part[i] = part_bytes(c->part_host[i], c->part_host[nparts + i]);
     return LOCUST_OK;
 }
@@ -598,9 +592,7 @@ int locust_shuffle_pack(locust_ctx *c, uint32_t nparts, void *dev_out, const uin
                                                  static_cast<uint8_t *>(dev_out), c->part_dev + 4ull * nparts, c->part_dev,
                                                  c->part_dev + 2ull * nparts, c->num_sms, c->stream);
     CU(cudaGetLastError());
-    // the host vector is read by the async copy: wait for it before the caller can call us again
-    CU(cudaStreamSynchronize(c->stream));
-    return LOCUST_OK;
+    return LOCUST_OK;      // (the offsets came from pageable memory: that copy was staged before it returned)
 }
 
 int locust_shuffle_begin_merge(locust_ctx *c) {
