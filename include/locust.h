@@ -112,12 +112,28 @@ int locust_result_device(locust_ctx *ctx, const uint8_t **key_blob, const uint64
                          const uint64_t **counts, const uint64_t **vals, uint64_t *n);
 
 /* printKeyIntValues (main.cu:126-134, line format :132)
- *   "print key: %s \t val: %d \t count: %d\n"
- * or, with cpu_format != 0, printKeyValues of the CPU branch (main.cu:286)
- *   "print key: %s \t value: %s\n".
+ *   LOCUST_FORMAT_GPU   "print key: %s \t val: %d \t count: %d\n"
+ * printKeyValues of the CPU branch (main.cu:286)
+ *   LOCUST_FORMAT_CPU   "print key: %s \t value: %s\n"
+ * writeKeyIntValues, the intermediate file of multi mode (main.cu:116-124, :121), with
+ * the combined count as the value
+ *   LOCUST_FORMAT_INTERMEDIATE   "%s \t%d\n".
  * Lines are formatted on the device and copied out in one piece.  Returns the
  * text through *text (borrowed, host memory, not NUL-terminated) and *nbytes. */
-int locust_format_result(locust_ctx *ctx, int cpu_format, const char **text, uint64_t *nbytes);
+#define LOCUST_FORMAT_GPU           0
+#define LOCUST_FORMAT_CPU           1
+#define LOCUST_FORMAT_INTERMEDIATE  2
+int locust_format_result(locust_ctx *ctx, int format, const char **text, uint64_t *nbytes);
+
+/* Replaces loadIntermediateFile (main.cu:66-103): adds the records of an intermediate
+ * text ("key \tvalue\n" lines, host memory) to the job, summing the values per key.  A
+ * file written by the reference's stage 1 has one line per token occurrence with value 1;
+ * a file written with LOCUST_FORMAT_INTERMEDIATE has one line per word with its count.
+ * Both reduce to the same result.  The single space the reference writes in front of the
+ * TAB is not part of the key (the reference keeps it, main.cu:94: its stage-2 keys end in a
+ * blank).  Lines are parsed on the host, the records are merged on the GPU.  Can be mixed
+ * with locust_map calls; follow with locust_process / locust_reduce. */
+int locust_map_intermediate(locust_ctx *ctx, const char *text, uint64_t nbytes);
 
 /* Device time of a stage in milliseconds (CUDA events on the context's stream):
  * what main.cu:408,:418,:468 print, but measured on the device. */

@@ -25,6 +25,7 @@ EXPORTS = [
     "locust_result_device", "locust_format_result", "locust_stage_ms", "locust_stats",
     "locust_last_error", "locust_shuffle_sizes", "locust_shuffle_pack",
     "locust_shuffle_begin_merge", "locust_shuffle_merge", "locust_count_static",
+    "locust_map_intermediate",
 ]
 STATIC_MAX_KEYS = 16384
 STATIC_MAX_BYTES = 1 << 32
@@ -77,6 +78,7 @@ def load():
     L.locust_shuffle_pack.argtypes = [vp, u32, vp, pp(u64)]
     L.locust_shuffle_begin_merge.argtypes = [vp]
     L.locust_shuffle_merge.argtypes = [vp, vp, u64]
+    L.locust_map_intermediate.argtypes = [vp, ctypes.c_char_p, u64]
     L.locust_count_static.argtypes = [vp, u64, vp, u64, pp(u64), vp, ctypes.c_char_p, ctypes.c_size_t]
     _lib = L
     return L
@@ -160,6 +162,11 @@ class WordCount:
         self._keep.append(keep)            # device inputs must outlive reduce()
         self._check(self._L.locust_map(self._h, ptr, n, where), "locust_map")
 
+    def map_intermediate(self, text):
+        """adds "key \\tvalue\\n" lines (the reference's /tmp/out.txt format, main.cu:121) to the job"""
+        b = bytes(text)
+        self._check(self._L.locust_map_intermediate(self._h, b, len(b)), "locust_map_intermediate")
+
     def process(self):
         self._check(self._L.locust_process(self._h), "locust_process")
 
@@ -213,10 +220,12 @@ class WordCount:
                                                  ctypes.byref(vals), ctypes.byref(n)), "locust_result_device")
         return blob.value, offs.value, cnts.value, vals.value, n.value
 
-    def format(self, cpu_format=False):
-        """The reference's `print key:` lines (main.cu:132, or :286 with cpu_format)."""
+    def format(self, cpu_format=False, intermediate=False):
+        """The reference's `print key:` lines (main.cu:132, or :286 with cpu_format), or the
+        intermediate "%s \\t%d\\n" lines of multi mode (main.cu:121)."""
         t, nb = ctypes.c_void_p(), ctypes.c_uint64()
-        self._check(self._L.locust_format_result(self._h, 1 if cpu_format else 0, ctypes.byref(t), ctypes.byref(nb)),
+        fmt = 2 if intermediate else (1 if cpu_format else 0)
+        self._check(self._L.locust_format_result(self._h, fmt, ctypes.byref(t), ctypes.byref(nb)),
                     "locust_format_result")
         return ctypes.string_at(t.value, nb.value) if nb.value else b""
 

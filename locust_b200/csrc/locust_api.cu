@@ -48,6 +48,7 @@ struct locust_ctx {
     std::vector<Segment> segments;
     bool cleared = false;           // table/counters zeroed for the current job
     bool shuffled = false;          // partials were packed; the table now holds merged records
+    bool replayable = true;         // the job can be redone from `segments` alone (false once records were merged in)
     int stage = 0;                  // 0 mapping, 1 processed, 2 reduced
 
     // host copies of the result (pinned)
@@ -235,7 +236,8 @@ int run_reduce_async(locust_ctx *c) {
 
 // Grows whatever the status bits name and runs MAP again over the recorded inputs.
 int grow_and_remap(locust_ctx *c, uint32_t st) {
-    if (c->shuffled) return fail(c, LOCUST_E_CAPACITY, "table too small for the merged partials; raise table_log2 / long_capacity");
+    if (c->shuffled || !c->replayable)
+        return fail(c, LOCUST_E_CAPACITY, "table too small for the merged records; raise table_log2 / long_capacity");
     int rc;
     if (st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull)) {
         uint64_t slots = c->slots, long_cap = c->long_cap;
@@ -386,6 +388,7 @@ int locust_reset(locust_ctx *c) {
     drop_segments(c);
     c->cleared = false;
     c->shuffled = false;
+    c->replayable = true;
     c->stage = 0;
     c->host_valid = false;
     for (auto &b : c->ev_set) b = false;
@@ -481,7 +484,7 @@ int locust_result_host(locust_ctx *c, const uint8_t **key_blob, const uint64_t *
 }
 
 int locust_format_result(locust_ctx *c, int cpu_format, const char **text, uint64_t *nbytes) {
-    if (!c || !text || !nbytes) return LOCUST_E_ARG;
+    if (!c || !text || !nbytes || cpu_format < 0 || cpu_format > 2) return LOCUST_E_ARG;
     if (c->stage != 2) return fail(c, LOCUST_E_STATE, "no result yet: run locust_reduce");
     CU(cudaSetDevice(c->device));
     const uint64_t n = c->h_ctr->n_out;
@@ -534,6 +537,64 @@ int locust_stats(locust_ctx *c, uint64_t *tokens, uint64_t *unique_keys, uint64_
 }
 
 const char *locust_last_error(locust_ctx *c) { return c ? c->err.c_str() : "null context"; }
+
+// ---- intermediate text of multi mode (main.cu:66-103) -----------------------------------------
+int locust_map_intermediate(locust_ctx *c, const char *text, uint64_t nbytes) {
+    if (!c || (!text && nbytes)) return LOCUST_E_ARG;
+    if (c->stage != 0) return fail(c, LOCUST_E_STATE, "locust_map_intermediate after locust_process; call locust_reset first");
+    CU(cudaSetDevice(c->device));
+    if (!c->cleared) {
+        CU(cudaEventRecord(c->ev[0], c->stream)); c->ev_set[0] = true;
+        int rc = clear_job(c);
+        if (rc) return rc;
+    }
+    // host: lines -> one packed part (header, 32-byte short records, long records)
+    std::vector<uint64_t> shorts;
+    std::vector<uint8_t> longs;
+    uint64_t i = 0;
+    while (i < nbytes) {
+        const char *nl = static_cast<const char *>(memchr(text + i, '\n', nbytes - i));
+        const uint64_t e = nl ? (uint64_t)(nl - text) : nbytes;
+        const char *tab = static_cast<const char *>(memchr(text + i, '\t', e - i));
+        if (tab) {
+            uint64_t klen = (uint64_t)(tab - (text + i));
+            if (klen && text[i + klen - 1] == ' ') --klen;              // the blank of "%s \t%d"
+            const long long v = strtoll(std::string(tab + 1, text + e).c_str(), nullptr, 10);
+            if (klen && v > 0) {
+                if (klen <= 16) {
+                    uint64_t k[2] = {0, 0};
+                    memcpy(k, text + i, klen);
+                    shorts.push_back(k[0]); shorts.push_back(k[1]); shorts.push_back((uint64_t)v); shorts.push_back(0);
+                } else {
+                    const uint64_t padded = (klen + 15) & ~15ull, at = longs.size();
+                    longs.resize(at + 16 + padded, 0);
+                    memcpy(&longs[at], &klen, 8);
+                    const uint64_t cnt = (uint64_t)v;
+                    memcpy(&longs[at + 8], &cnt, 8);
+                    memcpy(&longs[at + 16], text + i, klen);
+                }
+            }
+        }
+        i = e + 1;
+    }
+    const uint64_t n_short = shorts.size() / 4, total = (32 + 32 * n_short + longs.size() + 31) & ~31ull;
+    std::vector<uint8_t> part(total, 0);
+    const uint64_t hdr[4] = {n_short, (uint64_t)longs.size(), 0, 0};
+    memcpy(part.data(), hdr, 32);
+    if (n_short) memcpy(part.data() + 32, shorts.data(), 32 * n_short);
+    if (!longs.empty()) memcpy(part.data() + 32 + 32 * n_short, longs.data(), longs.size());
+    uint8_t *dev = nullptr;
+    CU(cudaMalloc(reinterpret_cast<void **>(&dev), total));
+    c->segments.push_back(Segment{dev, 0, dev});           // owned: long keys point into it until reset
+    CU(cudaMemcpyAsync(dev, part.data(), total, cudaMemcpyHostToDevice, c->stream));
+    MapParams p = map_params(c, dev, 0, 0);
+    c->launches += (uint64_t)launch_shuffle_merge(dev, total, p, c->num_sms, c->stream);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(c->stream));                    // `part` is about to go out of scope
+    c->replayable = false;
+    CU(cudaEventRecord(c->ev[1], c->stream)); c->ev_set[1] = true;
+    return LOCUST_OK;
+}
 
 // ---- multi-GPU shuffle ------------------------------------------------------------------
 static uint64_t part_bytes(uint64_t n_short, uint64_t long_bytes) {

@@ -8,6 +8,13 @@
 // the three stage-time lines (:408, :418, :468; here device-event times), one
 // "print key:" line per word (:132), "\nDone".  LOCUST_FORMAT=cpu switches the key
 // lines to the CPU branch's format (:286), which is what the parity oracle prints.
+//
+// Multi mode (main.cu:421-446): `stage` 1 maps the line window and writes the combined
+// (word, count) records as "%s \t%d\n" lines to /tmp/out.txt (LOCUST_INTERMEDIATE overrides
+// the path); `stage` 2 reads such a file -- also one written by the reference's own stage 1,
+// which holds one line per token -- and reduces it.  Inside one box the NCCL shuffle of
+// liblocust replaces this file hand-off; the stages are kept so the binary still fits the
+// reference's launcher (Distributor/slave.py starts it with these arguments).
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -50,10 +57,47 @@ int main(int argc, char *argv[]) {
         }
         stage = (int)strtol(argv[5], nullptr, 10);
     }
-    if (stage != 0) {
-        fprintf(stderr, "MapReduce: multi mode (stage %d) hands partials over with the NCCL shuffle of liblocust, "
-                        "not through /tmp/out.txt; run single mode.\n", stage);
+    if (stage != 0 && stage != 1 && stage != 2) {
+        fprintf(stderr, "MapReduce: stage must be 0 (single), 1 (map) or 2 (reduce)\n");
         return 2;
+    }
+    const char *inter_path = getenv("LOCUST_INTERMEDIATE") ? getenv("LOCUST_INTERMEDIATE") : "/tmp/out.txt";
+    const char *fmt_env = getenv("LOCUST_FORMAT");
+    const int key_format = (fmt_env && strcmp(fmt_env, "cpu") == 0) ? LOCUST_FORMAT_CPU : LOCUST_FORMAT_GPU;
+
+    locust_config cfg;
+    memset(&cfg, 0, sizeof cfg);
+    if (const char *d = getenv("LOCUST_DEVICE")) cfg.device = atoi(d);
+    if (const char *t = getenv("LOCUST_TABLE_LOG2")) cfg.table_log2 = (uint32_t)atoi(t);
+
+    if (stage == 2) {
+        // reduce stage: loadIntermediateFile (main.cu:441) + reduce (:447-473)
+        FILE *g = fopen(inter_path, "rb");
+        if (!g) { perror(inter_path); return 1; }
+        std::string text;
+        char tmp[1 << 16];
+        size_t got;
+        while ((got = fread(tmp, 1, sizeof tmp, g)) > 0) text.append(tmp, got);
+        fclose(g);
+        locust_ctx *ctx = nullptr;
+        int rc = locust_create(&cfg, &ctx);
+        if (rc) return die(ctx, "locust_create", rc);
+        rc = locust_map_intermediate(ctx, text.data(), text.size());
+        if (rc) return die(ctx, "locust_map_intermediate", rc);
+        rc = locust_process(ctx);
+        if (rc) return die(ctx, "locust_process", rc);
+        rc = locust_reduce(ctx);
+        if (rc) return die(ctx, "locust_reduce", rc);
+        printf("GPU reduce %d nanoseconds \n", (int)((locust_stage_ms(ctx, LOCUST_STAGE_PROCESS) +
+                                                      locust_stage_ms(ctx, LOCUST_STAGE_REDUCE)) * 1e6f));
+        const char *text_out = nullptr;
+        uint64_t nb = 0;
+        rc = locust_format_result(ctx, key_format, &text_out, &nb);
+        if (rc) return die(ctx, "locust_format_result", rc);
+        fwrite(text_out, 1, nb, stdout);
+        locust_destroy(ctx);
+        printf("\nDone\n");
+        return 0;
     }
 
     FILE *f = fopen(argv[1], "rb");
@@ -96,10 +140,6 @@ int main(int argc, char *argv[]) {
     }
     printf("Length: %i\n", (int)nlines);
 
-    locust_config cfg;
-    memset(&cfg, 0, sizeof cfg);
-    if (const char *d = getenv("LOCUST_DEVICE")) cfg.device = atoi(d);
-    if (const char *t = getenv("LOCUST_TABLE_LOG2")) cfg.table_log2 = (uint32_t)atoi(t);
     locust_ctx *ctx = nullptr;
     int rc = locust_create(&cfg, &ctx);
     if (rc) return die(ctx, "locust_create", rc);
@@ -112,12 +152,26 @@ int main(int argc, char *argv[]) {
     if (rc) return die(ctx, "locust_reduce", rc);
     printf("GPU mapping %d nanoseconds \n", (int)(locust_stage_ms(ctx, LOCUST_STAGE_MAP) * 1e6f));
     printf("GPU stream compaction and sorting %d nanoseconds \n", (int)(locust_stage_ms(ctx, LOCUST_STAGE_PROCESS) * 1e6f));
+    if (stage == 1) {
+        // map stage of multi mode: partials to the intermediate file, then exit (main.cu:421-432)
+        const char *lines = nullptr;
+        uint64_t nb = 0;
+        rc = locust_format_result(ctx, LOCUST_FORMAT_INTERMEDIATE, &lines, &nb);
+        if (rc) return die(ctx, "locust_format_result", rc);
+        FILE *g = fopen(inter_path, "wb");
+        if (!g) { perror(inter_path); return 1; }
+        fwrite(lines, 1, nb, g);
+        fclose(g);
+        locust_destroy(ctx);
+        cudaFreeHost(buf);
+        printf("MODE_MULTI: Finished map\n");
+        return 0;
+    }
     printf("GPU reduce %d nanoseconds \n", (int)(locust_stage_ms(ctx, LOCUST_STAGE_REDUCE) * 1e6f));
 
-    const char *fmt = getenv("LOCUST_FORMAT");
     const char *text = nullptr;
     uint64_t nbytes = 0;
-    rc = locust_format_result(ctx, fmt && strcmp(fmt, "cpu") == 0, &text, &nbytes);
+    rc = locust_format_result(ctx, key_format, &text, &nbytes);
     if (rc) return die(ctx, "locust_format_result", rc);
     fwrite(text, 1, nbytes, stdout);
     locust_destroy(ctx);

@@ -204,7 +204,8 @@ __global__ void __launch_bounds__(256) format_sizes_kernel(ReduceBufs o, const C
          k += (unsigned long long)gridDim.x * blockDim.x) {
         const uint64_t len = o.key_offsets[k + 1] - o.key_offsets[k];
         unsigned long long sz;
-        if (cpu_format) sz = 11 + len + 10 + dec_digits(o.counts[k]) + 1;
+        if (cpu_format == 2) sz = len + 2 + dec_digits(o.counts[k]) + 1;
+        else if (cpu_format) sz = 11 + len + 10 + dec_digits(o.counts[k]) + 1;
         else sz = 11 + len + 8 + dec_digits(o.vals[k]) + 10 + dec_digits(o.counts[k]) + 1;
         line_off[k] = sz;
     }
@@ -219,10 +220,13 @@ __global__ void __launch_bounds__(256) format_write_kernel(ReduceBufs o, Counter
         if (line_off[k + 1] > text_cap) { atomicOr(&ctr->status, kStatusTextFull); continue; }
         char *p = text + line_off[k];
         const uint64_t off = o.key_offsets[k], len = o.key_offsets[k + 1] - off;
-        p = put_str(p, "print key: ", 11);
+        if (cpu_format != 2) p = put_str(p, "print key: ", 11);
         for (uint64_t b = 0; b < len; ++b) p[b] = (char)o.key_blob[off + b];
         p += len;
-        if (cpu_format) {
+        if (cpu_format == 2) {                       // writeKeyIntValues, main.cu:121: "%s \t%d\n"
+            p = put_str(p, " \t", 2);
+            p = put_dec(p, o.counts[k]);
+        } else if (cpu_format) {
             p = put_str(p, " \t value: ", 10);
             p = put_dec(p, o.counts[k]);
         } else {

@@ -323,3 +323,52 @@ def test_cli_matches_reference_stdout(lb, tmp_path):
     want = pyoracle.wordcount(window).cpu_lines
     got = b"".join(l + b"\n" for l in r.split(b"\n") if l.startswith(b"print key: "))
     assert got == want and b"Using custom start and end locations: (10, 20)\nLength: 10\n" in r
+
+
+def test_intermediate_format_round_trip(lb, oracle):
+    """writeKeyIntValues / loadIntermediateFile (main.cu:116-124, :66-103): partials written as
+    "%s \\t%d\\n" lines and read back reduce to the same result; a file in the reference's own
+    stage-1 form (one line per token, value 1) does too."""
+    a, b = golden_input("hamlet"), golden_input("edge_long_tokens") + golden_input("rand_heavy_s4")
+    wc = lb.WordCount(device=0, table_log2=14)
+    wc.run(a)
+    inter_a = wc.format(intermediate=True)
+    keys, counts, _ = wc.result()
+    assert inter_a == b"".join(b"%s \t%d\n" % (k, c) for k, c in zip(keys, counts))
+    wc.run(b)
+    inter_b = wc.format(intermediate=True)
+    # two nodes' files merged by a reduce stage
+    wc.reset()
+    wc.map_intermediate(inter_a)
+    wc.map_intermediate(inter_b)
+    wc.process()
+    wc.reduce()
+    ref = oracle.wordcount(a + b"\n" + b)
+    assert wc.result()[:2] == (ref.keys, ref.counts)
+    # the reference's stage-1 file: every token on its own line with value 1, sorted
+    toks = sorted(t for t in re.split(b"[" + re.escape(DELIMS) + b"]+", b) if t)
+    ref_style = b"".join(t + b" \t1\n" for t in toks)
+    wc.reset()
+    wc.map_intermediate(ref_style)
+    wc.map(a)                                   # and it mixes with ordinary map calls
+    wc.process()
+    wc.reduce()
+    ref2 = oracle.wordcount(b + b"\n" + a)
+    assert wc.result()[:2] == (ref2.keys, ref2.counts)
+    wc.close()
+
+
+def test_cli_multi_mode_stages(lb, tmp_path):
+    exe = os.path.join(ROOT, "locust_b200", "MapReduce")
+    path = os.path.join(ROOT, "tests", "golden", "hamlet.txt")
+    inter = str(tmp_path / "out.txt")
+    env = dict(os.environ, LOCUST_FORMAT="cpu", LOCUST_TABLE_LOG2="14", LOCUST_INTERMEDIATE=inter)
+    s1 = subprocess.run([exe, path, "0", "100000", "0", "1"], capture_output=True, env=env, check=True).stdout
+    assert s1.endswith(b"MODE_MULTI: Finished map\n") and b"Done" not in s1 and b"print key" not in s1
+    with open(inter, "rb") as f:
+        first = f.readline()
+    assert first == b"&c \t1\n"
+    s2 = subprocess.run([exe, path, "0", "100000", "0", "2"], capture_output=True, env=env, check=True).stdout
+    assert s2.startswith(b"Running\nUsing custom start and end locations: (0, 100000)\nGPU reduce ") and s2.endswith(b"\n\nDone\n")
+    keylines = b"".join(l + b"\n" for l in s2.split(b"\n") if l.startswith(b"print key: "))
+    assert keylines == golden_ref_cpu("hamlet")
