@@ -603,6 +603,7 @@ static uint64_t part_bytes(uint64_t n_short, uint64_t long_bytes) {
 
 int locust_shuffle_sizes(locust_ctx *c, uint32_t nparts, uint64_t *bytes_per_part) {
     if (!c || !bytes_per_part || nparts == 0) return LOCUST_E_ARG;
+    if (nparts > 256) return fail(c, LOCUST_E_ARG, "locust_shuffle_sizes: at most 256 parts");
     if (c->stage != 0) return fail(c, LOCUST_E_STATE, "locust_shuffle_sizes after locust_process");
     CU(cudaSetDevice(c->device));
     if (!c->cleared) {            // nothing mapped on this rank: an empty job still takes part in the exchange

@@ -20,21 +20,32 @@ LC_D uint32_t part_of_long(const uint8_t *ptr, uint64_t len, uint32_t nparts) {
 }
 LC_D uint64_t long_record_bytes(uint64_t len) { return 16ull + ((len + 15ull) & ~15ull); }
 
+constexpr uint32_t kMaxParts = 256;
+
+// Both kernels first add up per part inside the block (shared-memory counters) and touch the
+// global per-part counters once per block and round: a million records would otherwise
+// serialise on a handful of addresses.
 __global__ void __launch_bounds__(256) shuffle_count_kernel(const Slot *__restrict__ table, uint64_t slots,
                                                             const LongOcc *__restrict__ long_list, uint64_t long_cap,
                                                             const Counters *ctr, uint32_t nparts,
                                                             unsigned long long *part_counts) {
+    __shared__ unsigned long long sh[2 * kMaxParts];
+    for (uint32_t i = threadIdx.x; i < 2 * nparts; i += blockDim.x) sh[i] = 0ull;
+    __syncthreads();
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < slots; i += stride) {
         const ulonglong2 k = *reinterpret_cast<const ulonglong2 *>(table + i);
-        if ((k.x | k.y) != 0ull) atomicAdd(&part_counts[part_of_short(k.x, k.y, nparts)], 1ull);
+        if ((k.x | k.y) != 0ull) atomicAdd(&sh[part_of_short(k.x, k.y, nparts)], 1ull);
     }
     unsigned long long nl = ctr->n_long;
     if (nl > long_cap) nl = long_cap;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nl; i += stride) {
         const LongOcc t = long_list[i];
-        atomicAdd(&part_counts[nparts + part_of_long(t.ptr, t.len, nparts)], long_record_bytes(t.len));
+        atomicAdd(&sh[nparts + part_of_long(t.ptr, t.len, nparts)], long_record_bytes(t.len));
     }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < 2 * nparts; i += blockDim.x)
+        if (sh[i]) atomicAdd(&part_counts[i], sh[i]);
 }
 
 __global__ void __launch_bounds__(256) shuffle_pack_kernel(const Slot *__restrict__ table, uint64_t slots,
@@ -43,20 +54,36 @@ __global__ void __launch_bounds__(256) shuffle_pack_kernel(const Slot *__restric
                                                            const unsigned long long *__restrict__ part_offsets,
                                                            const unsigned long long *__restrict__ part_counts,
                                                            unsigned long long *part_cursors) {
+    __shared__ unsigned long long sh_cnt[kMaxParts], sh_base[kMaxParts];
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (tid < nparts) {       // headers
         unsigned long long *h = reinterpret_cast<unsigned long long *>(out + part_offsets[tid]);
         h[0] = part_counts[tid]; h[1] = part_counts[nparts + tid]; h[2] = 0ull; h[3] = 0ull;
     }
-    for (uint64_t i = tid; i < slots; i += stride) {
-        const ulonglong4 v = *reinterpret_cast<const ulonglong4 *>(table + i);
-        if ((v.x | v.y) == 0ull) continue;
-        const uint32_t part = part_of_short(v.x, v.y, nparts);
-        const unsigned long long at = atomicAdd(&part_cursors[part], 1ull);
-        ulonglong4 *dst = reinterpret_cast<ulonglong4 *>(out + part_offsets[part] + 32ull) + at;
-        *dst = make_ulonglong4(v.x, v.y, v.z, 0ull);
+    // short records: every round the block reserves its records' places per part with one atomic
+    const uint64_t rounds = (slots + stride - 1) / stride;
+    for (uint64_t r = 0; r < rounds; ++r) {
+        for (uint32_t i = threadIdx.x; i < nparts; i += blockDim.x) sh_cnt[i] = 0ull;
+        __syncthreads();
+        const uint64_t i = r * stride + tid;
+        ulonglong4 v = make_ulonglong4(0ull, 0ull, 0ull, 0ull);
+        if (i < slots) v = *reinterpret_cast<const ulonglong4 *>(table + i);
+        const bool occ = (v.x | v.y) != 0ull;
+        uint32_t part = 0;
+        unsigned long long local = 0;
+        if (occ) { part = part_of_short(v.x, v.y, nparts); local = atomicAdd(&sh_cnt[part], 1ull); }
+        __syncthreads();
+        for (uint32_t q = threadIdx.x; q < nparts; q += blockDim.x)
+            sh_base[q] = sh_cnt[q] ? atomicAdd(&part_cursors[q], sh_cnt[q]) : 0ull;
+        __syncthreads();
+        if (occ) {
+            ulonglong4 *dst = reinterpret_cast<ulonglong4 *>(out + part_offsets[part] + 32ull) + sh_base[part] + local;
+            *dst = make_ulonglong4(v.x, v.y, v.z, 0ull);
+        }
+        __syncthreads();
     }
+    // long records (rare): one atomic each
     unsigned long long nl = ctr->n_long;
     if (nl > long_cap) nl = long_cap;
     for (uint64_t i = tid; i < nl; i += stride) {
