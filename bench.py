@@ -232,16 +232,21 @@ def main():
     avg_map_ms = sum(map_ms) / len(map_ms)
     peak, peak_src = measured_peak()
     achieved = alg_bytes / (avg_map_ms * 1e-3) / GB
-    traffic = None
-    tp = os.path.join(ROOT, "profiles", "map_kernel_traffic.json")
-    if os.path.exists(tp):
+    # DRAM bytes per launch from the committed `ncu --set full` capture of this kernel on this
+    # workload (profiles/rNN_map_kernel_traffic.json, written by tools/summarize_profiles.py)
+    traffic, traffic_src = None, None
+    import glob
+    for tp in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_map_kernel_traffic.json")), reverse=True):
         try:
             with open(tp) as f:
-                traffic = json.load(f).get("dram_bytes_per_launch")
+                t = json.load(f)
+            if world == 1 and t.get("input_bytes_of_capture") == per_gpu:
+                traffic, traffic_src = t.get("dram_bytes_per_launch"), os.path.relpath(tp, ROOT)
+                break
         except Exception:
-            traffic = None
+            pass
     roofline = {"bound": "hbm", "kernel": "tokenize_combine_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "avg_kernel_ms": avg_map_ms,
                 "map_share_of_step": avg_map_ms * args.steps / ms}
 
