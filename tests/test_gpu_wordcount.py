@@ -372,3 +372,57 @@ def test_cli_multi_mode_stages(lb, tmp_path):
     assert s2.startswith(b"Running\nUsing custom start and end locations: (0, 100000)\nGPU reduce ") and s2.endswith(b"\n\nDone\n")
     keylines = b"".join(l + b"\n" for l in s2.split(b"\n") if l.startswith(b"print key: "))
     assert keylines == golden_ref_cpu("hamlet")
+
+
+def _packed_keys(blob, offs):
+    """(n, 2) big-endian uint64 view of keys of <= 16 bytes, zero padded: integer order = key order"""
+    import numpy as np
+    offs = offs.astype(np.int64)
+    lens = np.diff(offs)
+    assert lens.min() >= 1 and lens.max() <= 16
+    keys = np.zeros((len(lens), 16), dtype=np.uint8)
+    idx = np.repeat(np.arange(len(lens)), lens)
+    within = np.arange(len(blob)) - np.repeat(offs[:-1], lens)
+    keys[idx, within] = blob
+    return keys.view(">u8").reshape(-1, 2).astype(np.uint64)
+
+
+@pytest.mark.parametrize("name,mib,log2", [("C3", 256, 20), ("C4", 128, 20), ("C5", 256, 20)])
+def test_larger_configs_by_properties(lb, name, mib, log2):
+    """Size-independent checks on the other BASELINE configurations at sizes the oracle would
+    need minutes for: strictly ascending keys, counts that add up to the token count, vals as
+    prefix sums, the two halves of the input adding up to the whole, and the combiner table
+    growing by itself (C4 starts 16x too small)."""
+    import numpy as np
+    from locust_b200.textgen import TextGen
+    n = mib << 20
+    g = TextGen.config(name, total_bytes=n, device=0)
+    d = torch.empty(n, dtype=torch.uint8, device="cuda")
+    g.fill_device(d)
+    torch.cuda.synchronize()
+    wc = lb.WordCount(device=0, table_log2=log2)
+
+    def run(view):
+        wc.run(view)
+        blob, offs, counts, vals = wc.result_arrays()
+        st = wc.stats()
+        assert int(counts.sum()) == st["tokens"] and len(counts) == st["unique_keys"]
+        assert (vals == np.concatenate([[0], np.cumsum(counts)[:-1]]).astype(np.uint64)).all()
+        k = _packed_keys(blob, offs)
+        a, b = k[:-1], k[1:]
+        assert ((a[:, 0] < b[:, 0]) | ((a[:, 0] == b[:, 0]) & (a[:, 1] < b[:, 1]))).all()      # sorted, unique
+        return k, counts
+
+    kw, cw = run(d)
+    half = n // 2                                  # a generator block boundary = a token boundary
+    k1, c1 = run(d[:half])
+    k2, c2 = run(d[half:])
+    k = np.concatenate([k1, k2])
+    c = np.concatenate([c1, c2])
+    order = np.lexsort((k[:, 1], k[:, 0]))
+    k, c = k[order], c[order]
+    head = np.ones(len(k), dtype=bool)
+    head[1:] = (k[1:] != k[:-1]).any(axis=1)
+    sums = np.add.reduceat(c, np.flatnonzero(head))
+    assert (k[head] == kw).all() and (sums == cw).all()
+    wc.close()
