@@ -51,6 +51,11 @@ extern "C" {
 #define LOCUST_F_GENERIC_TOKENISER  1u  /* test switch: byte-serial token path for every token */
 #define LOCUST_F_NO_SMEM_COMBINER   2u  /* test switch: every token goes to the global table     */
 #define LOCUST_F_WEAK_HASH          4u  /* test switch: 8-bit hashes, forces probe collisions    */
+#define LOCUST_F_SORT_PATH          8u  /* alternative path: no combiner; every token becomes a
+                                           record, PROCESS radix-sorts them all and REDUCE
+                                           run-length counts them -- what the reference does
+                                           (main.cu:406-465) without its fixed capacities.  Needs
+                                           table_log2 >= log2(tokens); slower, kept for comparison */
 
 typedef struct locust_ctx locust_ctx;
 

@@ -12,12 +12,12 @@ import ctypes
 import os
 
 __all__ = ["LocustError", "WordCount", "lib_path", "load", "HOST", "DEVICE",
-           "F_GENERIC_TOKENISER", "F_NO_SMEM_COMBINER", "F_WEAK_HASH"]
+           "F_GENERIC_TOKENISER", "F_NO_SMEM_COMBINER", "F_WEAK_HASH", "F_SORT_PATH"]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 HOST, DEVICE = 0, 1
 STAGE_MAP, STAGE_PROCESS, STAGE_REDUCE = 0, 1, 2
-F_GENERIC_TOKENISER, F_NO_SMEM_COMBINER, F_WEAK_HASH = 1, 2, 4
+F_GENERIC_TOKENISER, F_NO_SMEM_COMBINER, F_WEAK_HASH, F_SORT_PATH = 1, 2, 4, 8
 
 EXPORTS = [
     "locust_version", "locust_create", "locust_destroy", "locust_reset", "locust_map",

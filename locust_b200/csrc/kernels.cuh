@@ -45,17 +45,6 @@ struct Counters {
     uint32_t pass_src[16];          // buffer pass p reads (0 = A, 1 = B)
 };
 
-struct MapParams {
-    const uint8_t *base;        // 16-byte aligned; valid bytes are base[lo .. hi)
-    uint64_t lo, hi;
-    Slot *table;
-    uint64_t table_mask;        // slots - 1
-    LongOcc *long_list;
-    uint64_t long_cap;
-    Counters *ctr;
-    uint32_t flags;             // LOCUST_F_*
-};
-
 // Candidate records.  Sort buffers A/B hold (be0, be1, idx): the first 16 key
 // bytes big endian and zero padded (integer order = byte order, prefix first) and
 // the index of the record's payload (count, ref).
@@ -65,6 +54,18 @@ struct Records {
     unsigned long long *count;   // by payload index
     LongTok *ref;                // by payload index
     uint64_t cap;
+};
+
+struct MapParams {
+    const uint8_t *base;        // 16-byte aligned; valid bytes are base[lo .. hi)
+    uint64_t lo, hi;
+    Slot *table;
+    uint64_t table_mask;        // slots - 1
+    LongOcc *long_list;
+    uint64_t long_cap;
+    Counters *ctr;
+    uint32_t flags;             // LOCUST_F_*
+    Records rec;                // LOCUST_F_SORT_PATH only: every token becomes a record
 };
 
 struct SortScratch {
@@ -77,6 +78,7 @@ struct SortScratch {
 struct ReduceBufs {
     uint8_t *head;                   // cap flags
     unsigned long long *rank;        // cap
+    unsigned long long *csum;        // cap + 1: prefix sum over the counts in sorted order
     uint32_t *src_pos;               // cap: sorted position of each output key
     uint64_t *key_offsets;           // cap + 1
     unsigned long long *counts;      // cap

@@ -93,7 +93,7 @@ void free_record_buffers(locust_ctx *c) {
     cudaFree(c->rec.a0); cudaFree(c->rec.a1); cudaFree(c->rec.b0); cudaFree(c->rec.b1);
     cudaFree(c->rec.ia); cudaFree(c->rec.ib); cudaFree(c->rec.count); cudaFree(c->rec.ref);
     cudaFree(c->sort.lb_state);
-    cudaFree(c->red.head); cudaFree(c->red.rank); cudaFree(c->red.src_pos); cudaFree(c->red.key_offsets);
+    cudaFree(c->red.head); cudaFree(c->red.rank); cudaFree(c->red.csum); cudaFree(c->red.src_pos); cudaFree(c->red.key_offsets);
     cudaFree(c->red.counts); cudaFree(c->red.vals); cudaFree(c->red.key_blob);
     c->rec = Records{};
     c->red = ReduceBufs{};
@@ -119,7 +119,7 @@ int alloc_sized(locust_ctx *c, uint64_t slots, uint64_t long_cap) {
     CU(dalloc(&c->sort.lb_state, c->lb_words));
     CU(cudaMemsetAsync(c->sort.lb_state, 0, c->lb_words * sizeof(uint64_t), c->stream));
     c->epoch = 1;
-    CU(dalloc(&c->red.head, cap)); CU(dalloc(&c->red.rank, cap)); CU(dalloc(&c->red.src_pos, cap));
+    CU(dalloc(&c->red.head, cap)); CU(dalloc(&c->red.rank, cap)); CU(dalloc(&c->red.csum, cap + 1)); CU(dalloc(&c->red.src_pos, cap));
     CU(dalloc(&c->red.key_offsets, cap + 1)); CU(dalloc(&c->red.counts, cap)); CU(dalloc(&c->red.vals, cap));
     c->red.blob_cap = 16 * slots + 64 * long_cap;
     CU(dalloc(&c->red.key_blob, c->red.blob_cap));
@@ -165,6 +165,7 @@ MapParams map_params(locust_ctx *c, const uint8_t *dev, uint64_t lo_abs, uint64_
     p.long_cap = c->long_cap;
     p.ctr = c->ctr;
     p.flags = c->flags;
+    p.rec = c->rec;
     return p;
 }
 
@@ -243,7 +244,11 @@ int grow_and_remap(locust_ctx *c, uint32_t st) {
         uint64_t slots = c->slots, long_cap = c->long_cap;
         if (st & kStatusTableFull) slots *= 4;
         if (st & kStatusLongFull) { long_cap = c->h_ctr->n_long + (c->h_ctr->n_long >> 3) + 1024; }
-        if ((st & kStatusEntryFull) && !(st & (kStatusTableFull | kStatusLongFull))) slots *= 2;
+        if (st & kStatusEntryFull) {
+            // the record buffers hold slots + long_cap entries; n_entries kept counting past the end
+            const uint64_t need = c->h_ctr->n_entries + c->h_ctr->n_long + 1024;
+            while (slots + long_cap < need && slots < (1ull << 32)) slots *= 2;
+        }
         if (slots > (1ull << 32)) return fail(c, LOCUST_E_CAPACITY, "combiner table would exceed 2^32 slots");
         rc = alloc_sized(c, slots, long_cap);
         if (rc) return rc;

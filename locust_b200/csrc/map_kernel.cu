@@ -202,6 +202,30 @@ LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active
     uint32_t a, b, c, d;
     if (ascii) extract_key16_ascii(w0, w1, w2, w3, w4, o, L, a, b, c, d);      // warp-uniform branch
     else extract_key16_any(w0, w1, w2, w3, w4, o, L, a, b, c, d);
+    if (p.flags & LOCUST_F_SORT_PATH) {          // alternative path: one record per token, no combiner
+        const uint32_t m = __ballot_sync(kFull, has);
+        unsigned long long base = 0;
+        if (wc.lane == 0 && m) base = atomicAdd(&p.ctr->n_entries, (unsigned long long)__popc(m));
+        base = __shfl_sync(kFull, base, 0);
+        if (has) {
+            const unsigned long long e = base + __popc(m & ((1u << wc.lane) - 1u));
+            if (e < p.rec.cap) {
+                p.rec.a0[e] = bswap64((uint64_t)a | ((uint64_t)b << 32));
+                p.rec.a1[e] = bswap64((uint64_t)c | ((uint64_t)d << 32));
+                p.rec.ia[e] = (uint32_t)e;
+                p.rec.count[e] = 1ull;
+                p.rec.ref[e].ptr = nullptr;
+                p.rec.ref[e].len = L;
+            } else {
+                atomicOr(&p.ctr->status, kStatusEntryFull);
+            }
+        }
+        if (__any_sync(kFull, far)) {
+            if (far) token_generic(p, wc, row_pos + pos);
+            __syncwarp();
+        }
+        return;
+    }
     bool defer = has;
     if (has && L <= 8u && wc.use_smem) defer = !smem_insert(wc, a, b);
     const uint32_t m = __ballot_sync(kFull, defer);

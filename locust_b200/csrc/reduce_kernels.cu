@@ -114,11 +114,14 @@ __global__ void __launch_bounds__(256) head_kernel(Records r, ReduceBufs o, cons
         }
         o.head[i] = head ? 1 : 0;
         o.rank[i] = head ? 1ull : 0ull;
+        o.csum[i] = r.count[si[i]];                 // counts in sorted order, prefix-summed next
     }
 }
 
-// one thread per run head: merged count, key length, where the key sits
-__global__ void __launch_bounds__(256) run_sum_kernel(Records r, ReduceBufs o, const Counters *ctr) {
+// one thread per run head: where the key sits and how long it is.  The merged count of a run
+// is not summed here (a run can be millions of records long when every token is a record):
+// it is the difference of two entries of the prefix sum over the sorted counts.
+__global__ void __launch_bounds__(256) run_heads_kernel(Records r, ReduceBufs o, const Counters *ctr) {
     const unsigned long long n = ctr->n_entries;
     const bool in_b = ctr->sort_parity != 0u;
     const uint32_t *si = in_b ? r.ib : r.ia;
@@ -126,26 +129,27 @@ __global__ void __launch_bounds__(256) run_sum_kernel(Records r, ReduceBufs o, c
          i += (unsigned long long)gridDim.x * blockDim.x) {
         if (!o.head[i]) continue;
         const unsigned long long out = o.rank[i];
-        const uint32_t first = si[i];
-        unsigned long long sum = r.count[first];
-        for (unsigned long long j = i + 1; j < n && !o.head[j]; ++j) sum += r.count[si[j]];
-        o.counts[out] = sum;
-        o.vals[out] = sum;
-        o.key_offsets[out] = r.ref[first].len;
+        o.key_offsets[out] = r.ref[si[i]].len;
         o.src_pos[out] = (uint32_t)i;
     }
 }
 
+// per unique key: val = records in front of its run, count = records in its run (both weighted
+// by the records' counts), and the key bytes
 __global__ void __launch_bounds__(256) blob_kernel(Records r, ReduceBufs o, Counters *ctr) {
-    const unsigned long long n_out = ctr->n_out;
+    const unsigned long long n_out = ctr->n_out, n = ctr->n_entries;
     const bool in_b = ctr->sort_parity != 0u;
     const uint64_t *s0 = in_b ? r.b0 : r.a0, *s1 = in_b ? r.b1 : r.a1;
     const uint32_t *si = in_b ? r.ib : r.ia;
     for (unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; k < n_out;
          k += (unsigned long long)gridDim.x * blockDim.x) {
+        const uint32_t pos = o.src_pos[k];
+        const unsigned long long before = o.csum[pos];
+        const unsigned long long upto = k + 1 < n_out ? o.csum[o.src_pos[k + 1]] : o.csum[n];
+        o.vals[k] = before;
+        o.counts[k] = upto - before;
         const uint64_t off = o.key_offsets[k], len = o.key_offsets[k + 1] - off;
         if (off + len > o.blob_cap) { atomicOr(&ctr->status, kStatusBlobFull); continue; }
-        const uint32_t pos = o.src_pos[k];
         uint8_t *dst = o.key_blob + off;
         if (len <= 16) {
             const uint64_t b0 = s0[pos], b1 = s1[pos];
@@ -168,14 +172,15 @@ int launch_reduce(Records r, SortScratch s, ReduceBufs o, Counters *ctr, uint32_
     int k = 1;
     k += launch_exclusive_scan_u64(o.rank, o.rank, &ctr->n_entries, r.cap, s.lb_state, s.tickets + 32, epoch,
                                    &ctr->n_out, false, num_sms, st);
-    run_sum_kernel<<<(unsigned)g, 256, 0, st>>>(r, o, ctr);
+    // prefix sum over the sorted counts (entry n = sum of all counts = tokens)
+    k += launch_exclusive_scan_u64(o.csum, o.csum, &ctr->n_entries, r.cap, s.lb_state, s.tickets + 36, epoch + 2,
+                                   &ctr->total, true, num_sms, st);
+    run_heads_kernel<<<(unsigned)g, 256, 0, st>>>(r, o, ctr);
     k += 1;
-    // key lengths -> offsets (n_out + 1 entries); counts -> vals
+    // key lengths -> offsets (n_out + 1 entries)
     k += launch_exclusive_scan_u64(reinterpret_cast<unsigned long long *>(o.key_offsets),
                                    reinterpret_cast<unsigned long long *>(o.key_offsets), &ctr->n_out, r.cap,
                                    s.lb_state, s.tickets + 34, epoch + 1, &ctr->blob_bytes, true, num_sms, st);
-    k += launch_exclusive_scan_u64(o.vals, o.vals, &ctr->n_out, r.cap, s.lb_state, s.tickets + 36, epoch + 2,
-                                   &ctr->total, false, num_sms, st);
     blob_kernel<<<(unsigned)g, 256, 0, st>>>(r, o, ctr);
     k += 1;
     return k;

@@ -95,13 +95,14 @@ def test_gpu_branch_line_format(lb):
     wc.close()
 
 
-FLAG_SETS = [0, 1, 2, 3, 4, 6, 7]
+FLAG_SETS = [0, 1, 2, 3, 4, 6, 7, 8, 9]
 
 
 @pytest.mark.parametrize("flags", FLAG_SETS)
 @pytest.mark.parametrize("name", ["hamlet", "edge_basic", "edge_long_tokens", "rand_heavy_s4", "rand_print_s3"])
 def test_every_code_path_agrees(lb, oracle, name, flags):
-    # 1: byte-serial tokeniser, 2: no shared-memory combiner, 4: 8-bit hash (forced collisions)
+    # 1: byte-serial tokeniser, 2: no shared-memory combiner, 4: 8-bit hash (forced collisions),
+    # 8: alternative path (every token a record, radix sort + run-length reduce, no combiner)
     check_against_oracle(lb, oracle, golden_input(name), flags=flags, table_log2=14)
 
 
@@ -169,6 +170,12 @@ def test_long_tokens(lb, oracle):
     ref = check_against_oracle(lb, oracle, data, "device", table_log2=12)
     assert max(len(k) for k in ref.keys) == 70000
     check_against_oracle(lb, oracle, data, "host", table_log2=12, long_capacity=4)      # forces the long buffer to grow
+
+
+def test_sort_path_matches_and_grows(lb, oracle):
+    # the alternative path needs one record per token: 16 slots + 4 long entries must grow a lot
+    data = golden_input("rand_heavy_s4") + golden_input("edge_long_tokens")
+    check_against_oracle(lb, oracle, data, "device", table_log2=4, long_capacity=4, flags=8)
 
 
 def test_table_growth(lb, oracle):
