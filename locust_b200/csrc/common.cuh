@@ -47,10 +47,9 @@ LC_HD uint32_t classify4(uint32_t x) {
     return (a ^ b ^ c) & ~x & 0x80808080u;
 }
 
-// Gathers the four 0x80 flags of classify4 into bits 0..3.
-LC_HD uint32_t gather4(uint32_t flags) { return (flags * 0x00204081u) >> 28; }
-
-// 16-bit delimiter mask of a 16-byte chunk (bit i = byte i is a delimiter).
+// 16-bit delimiter mask of a 16-byte chunk (bit i = byte i is a delimiter): the four 0x80
+// flags of each word are gathered into a nibble by one multiply (0x00204081 moves bits
+// 7, 15, 23, 31 to bits 28..31 without carries).
 LC_HD uint32_t classify16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
     const uint32_t p0 = classify4(w0) * 0x00204081u;
     const uint32_t p1 = classify4(w1) * 0x00204081u;
@@ -80,23 +79,11 @@ LC_HD uint32_t byte_perm(uint32_t a, uint32_t b, uint32_t s) {
 #endif
 }
 
-// Key of a token of L <= 8 ASCII bytes starting at byte `o` (0..3) of word wa,
-// with wb, wc the following words: the token's bytes, zero padded, as a
-// little-endian 64-bit value (lo = bytes 0..3, hi = bytes 4..7).  Bytes past L
-// are zeroed by setting bit 3 of their selector nibble, which yields 0x00 for any
-// byte below 0x80 -- callers only use this on all-ASCII chunks.
-LC_HD void extract_key8(uint32_t wa, uint32_t wb, uint32_t wc, uint32_t o, uint32_t L,
-                        uint32_t &lo, uint32_t &hi) {
-    const uint32_t sel = 0x3210u + 0x1111u * o;
-    const uint32_t z = (L >= 8u) ? 0u : (0x88888888u << (4u * L));
-    lo = byte_perm(wa, wb, sel | (z & 0xFFFFu));
-    hi = byte_perm(wb, wc, sel | (z >> 16));
-}
-
 // Key of a token of L <= 16 bytes starting at byte `o` (0..3) of word w0, with
 // w1..w4 the following words: four little-endian words, zero padded past L.
 // ASCII variant (every byte of the window < 0x80): bytes past L are zeroed inside
-// the PRMT by the sign-replicate bit, as in extract_key8.
+// the PRMT -- bit 3 of a selector nibble replicates the selected byte's sign bit,
+// which is 0x00 for any byte below 0x80.
 LC_HD void key_selectors(uint32_t o, uint32_t L, uint32_t &sel, uint32_t &zlo, uint32_t &zhi) {
     sel = 0x3210u + 0x1111u * o;
     zlo = (L >= 8u) ? 0u : (0x88888888u << (4u * L));
@@ -123,9 +110,6 @@ LC_HD void extract_key16_any(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3,
     d = byte_perm(w3, w4, sel) & byte_perm(0xFFu, 0u, zhi >> 19);
 }
 
-// Index of the lowest set bit of a 4-bit value (0 for 0), from a 32-bit table.
-LC_HD uint32_t low_bit4(uint32_t n) { return (0x12131210u >> (2u * n)) & 3u; }
-
 LC_HD uint64_t bswap64(uint64_t v) {
     v = ((v & 0x00FF00FF00FF00FFull) << 8) | ((v >> 8) & 0x00FF00FF00FF00FFull);
     v = ((v & 0x0000FFFF0000FFFFull) << 16) | ((v >> 16) & 0x0000FFFF0000FFFFull);
@@ -151,14 +135,6 @@ struct __align__(32) Slot {
     uint64_t k0, k1;
     unsigned long long count;
     uint64_t pad;
-};
-
-// A sorted/unsorted record of the process stage: be0/be1 = first 16 key bytes,
-// big endian and zero padded (so integer order = byte order, prefix first);
-// for keys longer than 16 bytes `ptr` addresses the full key and len > 16.
-struct __align__(16) LongRef {
-    const uint8_t *ptr;
-    uint64_t len;
 };
 
 }  // namespace locust

@@ -26,7 +26,6 @@ int main() {
                     const unsigned byte = (w >> (8 * b)) & 0xFF;
                     if ((((f >> (8 * b + 7)) & 1u) != 0) != naive_delim(byte)) { printf("classify4 %08x byte %d\n", w, b); return 1; }
                 }
-                if (gather4(f) != (((f >> 7) & 1) | ((f >> 14) & 2) | ((f >> 21) & 4) | ((f >> 28) & 8))) { printf("gather4\n"); return 1; }
             }
     // classify16
     for (int t = 0; t < 200000; ++t) {
@@ -38,21 +37,6 @@ int main() {
         for (int i = 0; i < 16; ++i)
             if (((d >> i) & 1u) != (naive_delim(b[i]) ? 1u : 0u)) { printf("classify16 bit %d\n", i); return 1; }
         if (d >> 16) { printf("classify16 high bits\n"); return 1; }
-    }
-    // extract_key8: all start offsets and lengths over ASCII data
-    for (int t = 0; t < 100000; ++t) {
-        uint8_t b[12];
-        for (auto &x : b) x = (uint8_t)(1 + rnd() % 127);
-        uint32_t w[3];
-        memcpy(w, b, 12);
-        for (uint32_t o = 0; o < 4; ++o)
-            for (uint32_t L = 1; L <= 8; ++L) {
-                uint32_t lo, hi;
-                extract_key8(w[0], w[1], w[2], o, L, lo, hi);
-                uint64_t want = 0;
-                for (uint32_t i = 0; i < L; ++i) want |= (uint64_t)b[o + i] << (8 * i);
-                if ((((uint64_t)hi << 32) | lo) != want) { printf("extract_key8 o=%u L=%u\n", o, L); return 1; }
-            }
     }
     // extract_key16_*: all start offsets and lengths 1..16; the ASCII variant on ASCII data,
     // the general variant on every byte value except NUL
@@ -74,8 +58,6 @@ int main() {
                 if (memcmp(q, wantg, 16) != 0) { printf("extract_key16_any o=%u L=%u\n", o, L); return 1; }
             }
     }
-    for (uint32_t n = 1; n < 16; ++n)
-        if (low_bit4(n) != (uint32_t)__builtin_ctz(n)) { printf("low_bit4 %u\n", n); return 1; }
     if (bswap64(0x0102030405060708ull) != 0x0807060504030201ull) { printf("bswap64\n"); return 1; }
     printf("ok\n");
     return 0;
