@@ -77,18 +77,20 @@ __device__ __noinline__ void global_insert(const MapParams &p, uint64_t k0, uint
     atomicOr(&p.ctr->status, kStatusTableFull);
 }
 
-// Per-warp view of shared memory.
+// Per-warp view of shared memory, kept as 32-bit offsets into the CTA's dynamic shared memory.
+extern __shared__ __align__(16) uint8_t smem_raw[];
 struct WarpCtx {
-    ulonglong2 *skeys;     // kBuckets buckets {key way 0, key way 1}
-    uint32_t *scnt;        // 2 * kBuckets counters
-    uint8_t *row;          // staged row + look-ahead
-    uint32_t *bits;        // delimiter bits of the row + look-ahead
-    uint16_t *desc;        // positions of token starts
-    ulonglong2 *queue;     // keys waiting for the global table
+    uint32_t area;         // byte offset of this warp's area
     uint32_t qn;           // entries queued (warp-uniform)
     uint32_t lane;
     bool use_smem;
 };
+#define WC_SKEYS reinterpret_cast<ulonglong2 *>(smem_raw)
+#define WC_SCNT reinterpret_cast<uint32_t *>(smem_raw + kKeysBytes)
+#define WC_ROW(wc) (smem_raw + (wc).area + kRowOff)
+#define WC_BITS(wc) reinterpret_cast<uint32_t *>(smem_raw + (wc).area + kBitsOff)
+#define WC_DESC(wc) reinterpret_cast<uint16_t *>(smem_raw + (wc).area + kDescOff)
+#define WC_QUEUE(wc) reinterpret_cast<ulonglong2 *>(smem_raw + (wc).area + kQueueOff)
 
 // Counts a token of <= 8 bytes (key = lo | hi << 32, never 0) in the CTA's table.
 // One 128-bit load reads both ways of the bucket.  False if the bucket is taken by
@@ -97,14 +99,14 @@ LC_D bool smem_insert(const WarpCtx &wc, uint32_t lo, uint32_t hi) {
     const uint32_t h = lo * 0x9E3779B1u + hi * 0x85EBCA77u;
     const uint32_t b = __umulhi(h, kBuckets);
     const unsigned long long k = (unsigned long long)lo | ((unsigned long long)hi << 32);
-    const ulonglong2 kb = wc.skeys[b];
-    if (kb.x == k) { atomicAdd(&wc.scnt[2 * b], 1u); return true; }
-    if (kb.y == k) { atomicAdd(&wc.scnt[2 * b + 1], 1u); return true; }
+    const ulonglong2 kb = WC_SKEYS[b];
+    if (kb.x == k) { atomicAdd(&WC_SCNT[2 * b], 1u); return true; }
+    if (kb.y == k) { atomicAdd(&WC_SCNT[2 * b + 1], 1u); return true; }
     if (kb.x == 0ull || kb.y == 0ull) {
         const uint32_t way = kb.x == 0ull ? 0u : 1u;
-        unsigned long long *slot = reinterpret_cast<unsigned long long *>(wc.skeys) + 2 * b + way;
+        unsigned long long *slot = reinterpret_cast<unsigned long long *>(WC_SKEYS) + 2 * b + way;
         const unsigned long long old = atomicCAS(slot, 0ull, k);
-        if (old == 0ull || old == k) { atomicAdd(&wc.scnt[2 * b + way], 1u); return true; }
+        if (old == 0ull || old == k) { atomicAdd(&WC_SCNT[2 * b + way], 1u); return true; }
     }
     return false;
 }
@@ -168,7 +170,7 @@ LC_D void drain_queue(const MapParams &p, WarpCtx &wc, uint32_t keep_below) {
         const uint32_t take = wc.qn < 32u ? wc.qn : 32u;
         const bool valid = wc.lane < take;
         ulonglong2 k = make_ulonglong2(0ull, 0ull);
-        if (valid) k = wc.queue[wc.qn - take + wc.lane];
+        if (valid) k = WC_QUEUE(wc)[wc.qn - take + wc.lane];
         const uint32_t h = (uint32_t)k.x * 0x9E3779B1u + (uint32_t)(k.x >> 32) * 0x85EBCA77u +
                            (uint32_t)k.y * 0xC2B2AE3Du + (uint32_t)(k.y >> 32) * 0x27D4EB2Fu;
         const uint32_t peers = __match_any_sync(kFull, h);
@@ -188,11 +190,11 @@ LC_D void drain_queue(const MapParams &p, WarpCtx &wc, uint32_t keep_below) {
 // Phase B for one batch: lane `wc.lane` takes token number t of the row (if active).
 // All lanes call this together.
 LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active, uint32_t t, uint64_t row_pos) {
-    const uint32_t *row32 = reinterpret_cast<const uint32_t *>(wc.row);
-    const uint32_t pos = active ? wc.desc[t] : 0u;
+    const uint32_t *row32 = reinterpret_cast<const uint32_t *>(WC_ROW(wc));
+    const uint32_t pos = active ? WC_DESC(wc)[t] : 0u;
     // token length: first delimiter at or after pos, within 17 bits
     const uint32_t wi = pos >> 5;
-    const uint32_t win = __funnelshift_r(wc.bits[wi], wc.bits[wi + 1], pos & 31u) & 0x1FFFFu;
+    const uint32_t win = __funnelshift_r(WC_BITS(wc)[wi], WC_BITS(wc)[wi + 1], pos & 31u) & 0x1FFFFu;
     const uint32_t L = (uint32_t)__ffs((int)win) - 1u;            // win == 0 -> 0xFFFFFFFF
     const bool has = active && win != 0u;
     const bool far = active && win == 0u;
@@ -231,7 +233,7 @@ LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active
     const uint32_t m = __ballot_sync(kFull, defer);
     if (m) {
         if (defer)
-            wc.queue[wc.qn + __popc(m & ((1u << wc.lane) - 1u))] =
+            WC_QUEUE(wc)[wc.qn + __popc(m & ((1u << wc.lane) - 1u))] =
                 make_ulonglong2((uint64_t)a | ((uint64_t)b << 32), (uint64_t)c | ((uint64_t)d << 32));
         wc.qn += __popc(m);
         if (wc.qn >= 32u) drain_queue(p, wc, 32u);
@@ -243,7 +245,6 @@ LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active
 }
 
 __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const __grid_constant__ MapParams p) {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
     {
         uint4 *z = reinterpret_cast<uint4 *>(smem_raw);
         for (uint32_t i = threadIdx.x; i < (kKeysBytes + kCntBytes) / 16; i += kMapThreads) z[i] = make_uint4(0, 0, 0, 0);
@@ -261,19 +262,12 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
     const uint64_t seg_len = (nrows + nwarps * kSegments - 1) / (nwarps * kSegments);
     const bool use_fast = !(p.flags & LOCUST_F_GENERIC_TOKENISER);
     WarpCtx wc;
-    wc.skeys = reinterpret_cast<ulonglong2 *>(smem_raw);
-    wc.scnt = reinterpret_cast<uint32_t *>(smem_raw + kKeysBytes);
-    uint8_t *area = smem_raw + kKeysBytes + kCntBytes + warp * kWarpArea;
-    wc.row = area + kRowOff;
-    wc.bits = reinterpret_cast<uint32_t *>(area + kBitsOff);
-    wc.desc = reinterpret_cast<uint16_t *>(area + kDescOff);
-    wc.queue = reinterpret_cast<ulonglong2 *>(area + kQueueOff);
+    wc.area = kKeysBytes + kCntBytes + warp * kWarpArea;
     wc.qn = 0u;
     wc.lane = lane;
     wc.use_smem = !(p.flags & LOCUST_F_NO_SMEM_COMBINER);
-    uint16_t *bits16 = reinterpret_cast<uint16_t *>(wc.bits);
+    uint16_t *bits16 = reinterpret_cast<uint16_t *>(WC_BITS(wc));
 
-#pragma unroll 1
     for (uint32_t seg = 0; seg < kSegments; ++seg) {
         const uint64_t r0 = row_lo + (seg * nwarps + gw) * seg_len;
         uint64_t r1 = r0 + seg_len;
@@ -298,8 +292,8 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
             const uint64_t row_pos = row * 512ull;
             if (use_fast) {
                 // A: stage bytes and delimiter bits (with the next row's first chunks as look-ahead)
-                reinterpret_cast<uint4 *>(wc.row)[lane] = c;
-                if (lane < 2) reinterpret_cast<uint4 *>(wc.row)[32 + lane] = n;
+                reinterpret_cast<uint4 *>(WC_ROW(wc))[lane] = c;
+                if (lane < 2) reinterpret_cast<uint4 *>(WC_ROW(wc))[32 + lane] = n;
                 bits16[lane] = (uint16_t)dc;
                 if (lane < 4) bits16[32 + lane] = (uint16_t)dn;
                 // dense list of token starts: warp prefix sum of the per-lane counts
@@ -313,7 +307,7 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
                 const uint32_t total = __shfl_sync(kFull, incl, 31);
                 uint32_t at = incl - cnt;
                 while (starts) {
-                    wc.desc[at++] = (uint16_t)(lane * 16u + (uint32_t)__ffs((int)starts) - 1u);
+                    WC_DESC(wc)[at++] = (uint16_t)(lane * 16u + (uint32_t)__ffs((int)starts) - 1u);
                     starts &= starts - 1u;
                 }
                 __syncwarp();
@@ -339,10 +333,10 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
     drain_queue(p, wc, 1u);
     __syncthreads();
     // flush the CTA's combiner into the global table
-    const unsigned long long *keys = reinterpret_cast<const unsigned long long *>(wc.skeys);
+    const unsigned long long *keys = reinterpret_cast<const unsigned long long *>(WC_SKEYS);
     for (uint32_t i = threadIdx.x; i < kSmemSlots; i += kMapThreads) {
         const unsigned long long k = keys[i];
-        if (k) global_insert(p, k, 0ull, (unsigned long long)wc.scnt[i]);
+        if (k) global_insert(p, k, 0ull, (unsigned long long)WC_SCNT[i]);
     }
 }
 
