@@ -138,6 +138,9 @@ def main():
     ap.add_argument("--cpu-sample-mib", type=int, default=32)
     ap.add_argument("--table-log2", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--shuffle", default="peers", choices=["peers", "nccl"],
+                    help="N>1: 'peers' = packing kernel writes into the destination GPU's memory over NVLink "
+                         "(fused pack+send), 'nccl' = pack locally, all_to_all_single")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -178,8 +181,10 @@ def main():
     table_log2 = args.table_log2 or (17 if name == "C2" else 22)
     wc = locust_b200.WordCount(device=local_rank, table_log2=table_log2, stream=stream.cuda_stream)
     if world > 1:
-        from locust_b200.shuffle import DistributedWordCount, GpuBackend
-        job = DistributedWordCount(GpuBackend(wc, dev), dist)
+        from locust_b200.shuffle import DistributedWordCount, GpuBackend, PeerExchange
+        with torch.cuda.stream(stream):
+            peers = PeerExchange(wc, dist, dev, 1 << table_log2) if args.shuffle == "peers" else None
+        job = DistributedWordCount(GpuBackend(wc, dev), dist, peers=peers)
         step = lambda buf: job.run(buf)
     else:
         step = lambda buf: wc.run(buf)
@@ -256,8 +261,15 @@ def main():
         # rank sent to other ranks in the hash shuffle.  770 GB/s = measured peer copy per direction
         # (B200_PROFILING.md); the shuffle here is latency-, not bandwidth-bound.
         sms_, sb_ = sum(x for x, _ in shuf) / len(shuf), sum(b for _, b in shuf) / len(shuf)
-        shuffle = {"ms": sms_, "bytes_sent_rank0": sb_, "achieved_gbs": sb_ / (sms_ * 1e-3) / GB if sms_ > 0 else None,
-                   "peak_gbs": 770.0, "frac": (sb_ / (sms_ * 1e-3) / GB / 770.0) if sms_ > 0 else None}
+        if args.shuffle == "peers":
+            # fused pack+send: the packing kernel stores every record in the destination GPU's memory; no
+            # sizes are exchanged, so the bytes sent are not known on the host
+            shuffle = {"path": "peers (pack kernel writes over NVLink peer memory, one all-reduce barrier per exchange)",
+                       "ms": sms_, "bytes_sent_rank0": None, "achieved_gbs": None, "peak_gbs": 770.0, "frac": None}
+        else:
+            shuffle = {"path": "nccl (local pack, all_to_all_single of sizes and records)", "ms": sms_,
+                       "bytes_sent_rank0": sb_, "achieved_gbs": sb_ / (sms_ * 1e-3) / GB if sms_ > 0 else None,
+                       "peak_gbs": 770.0, "frac": (sb_ / (sms_ * 1e-3) / GB / 770.0) if sms_ > 0 else None}
 
     # ---- end to end: pinned host input in, host result out, every step ---------------------
     host = torch.empty(per_gpu, dtype=torch.uint8, pin_memory=True)

@@ -163,6 +163,27 @@ int locust_shuffle_sizes(locust_ctx *ctx, uint32_t nparts, uint64_t *bytes_per_p
  * and sizes as reported by locust_shuffle_sizes, each a multiple of 32). */
 int locust_shuffle_pack(locust_ctx *ctx, uint32_t nparts, void *dev_out, const uint64_t *part_offsets);
 
+/* ---- pack and send in one kernel, over peer memory (NVLink) ---------------------------------
+ * Instead of packing into a local buffer and handing that to a collective, part p is written
+ * straight into a slot of rank p's receive buffer by the packing kernel itself.  No sizes are
+ * exchanged: a slot is `slot_bytes` long, holds up to `short_cap` short records at byte 32 and
+ * long records behind them, and its 32-byte header (written last) says how much arrived.  The
+ * caller separates pack and merge by a barrier over all ranks on the context's stream (e.g. a
+ * one-element all-reduce), then merges every slot of its own buffer with locust_shuffle_merge
+ * (dev_records = slot, nbytes = slot_bytes).  short_cap = the sender's table size cannot
+ * overflow; long records that do not fit make locust_reduce fail with LOCUST_E_CAPACITY.
+ * Note: MAP's own buffers are not re-grown on this path -- size table_log2 for the shard.
+ *
+ * locust_exchange_alloc: a zeroed receive buffer on ctx's device, owned by ctx.
+ * locust_ipc_export / _open / _close: the 64-byte handle another process on the same box needs
+ * to map that buffer (cudaIpcGetMemHandle / OpenMemHandle / CloseMemHandle). */
+int locust_exchange_alloc(locust_ctx *ctx, uint64_t nbytes, void **dev_buf);
+int locust_ipc_export(locust_ctx *ctx, const void *dev_buf, uint8_t handle[64]);
+int locust_ipc_open(locust_ctx *ctx, const uint8_t handle[64], void **dev_buf);
+int locust_ipc_close(locust_ctx *ctx, void *dev_buf);
+int locust_shuffle_pack_peers(locust_ctx *ctx, uint32_t nparts, void *const *dst_slots, uint64_t slot_bytes,
+                              uint64_t short_cap);
+
 /* Drops the local partials (they have been packed) and starts the final table. */
 int locust_shuffle_begin_merge(locust_ctx *ctx);
 

@@ -25,7 +25,8 @@ EXPORTS = [
     "locust_result_device", "locust_format_result", "locust_stage_ms", "locust_stats",
     "locust_last_error", "locust_shuffle_sizes", "locust_shuffle_pack",
     "locust_shuffle_begin_merge", "locust_shuffle_merge", "locust_count_static",
-    "locust_map_intermediate",
+    "locust_map_intermediate", "locust_exchange_alloc", "locust_ipc_export", "locust_ipc_open", "locust_ipc_close",
+    "locust_shuffle_pack_peers",
 ]
 STATIC_MAX_KEYS = 16384
 STATIC_MAX_BYTES = 1 << 32
@@ -79,6 +80,11 @@ def load():
     L.locust_shuffle_begin_merge.argtypes = [vp]
     L.locust_shuffle_merge.argtypes = [vp, vp, u64]
     L.locust_map_intermediate.argtypes = [vp, ctypes.c_char_p, u64]
+    L.locust_exchange_alloc.argtypes = [vp, u64, pp(vp)]
+    L.locust_ipc_export.argtypes = [vp, vp, ctypes.c_char_p]
+    L.locust_ipc_open.argtypes = [vp, ctypes.c_char_p, pp(vp)]
+    L.locust_ipc_close.argtypes = [vp, vp]
+    L.locust_shuffle_pack_peers.argtypes = [vp, u32, pp(vp), u64, u64]
     L.locust_count_static.argtypes = [vp, u64, vp, u64, pp(u64), vp, ctypes.c_char_p, ctypes.c_size_t]
     _lib = L
     return L
@@ -251,6 +257,31 @@ class WordCount:
     def shuffle_pack(self, nparts, dev_out_ptr, part_offsets):
         arr = (ctypes.c_uint64 * nparts)(*part_offsets)
         self._check(self._L.locust_shuffle_pack(self._h, nparts, dev_out_ptr, arr), "locust_shuffle_pack")
+
+    # -- pack + send in one kernel over peer memory ---------------------------------------
+    def exchange_alloc(self, nbytes):
+        """zeroed receive buffer on this context's device (freed with the context); device address"""
+        p = ctypes.c_void_p()
+        self._check(self._L.locust_exchange_alloc(self._h, nbytes, ctypes.byref(p)), "locust_exchange_alloc")
+        return p.value
+
+    def ipc_export(self, dev_ptr):
+        h = ctypes.create_string_buffer(64)
+        self._check(self._L.locust_ipc_export(self._h, dev_ptr, h), "locust_ipc_export")
+        return h.raw
+
+    def ipc_open(self, handle):
+        p = ctypes.c_void_p()
+        self._check(self._L.locust_ipc_open(self._h, bytes(handle), ctypes.byref(p)), "locust_ipc_open")
+        return p.value
+
+    def ipc_close(self, dev_ptr):
+        self._check(self._L.locust_ipc_close(self._h, dev_ptr), "locust_ipc_close")
+
+    def shuffle_pack_peers(self, dst_slots, slot_bytes, short_cap):
+        arr = (ctypes.c_void_p * len(dst_slots))(*dst_slots)
+        self._check(self._L.locust_shuffle_pack_peers(self._h, len(dst_slots), arr, slot_bytes, short_cap),
+                    "locust_shuffle_pack_peers")
 
     def shuffle_begin_merge(self):
         self._check(self._L.locust_shuffle_begin_merge(self._h), "locust_shuffle_begin_merge")

@@ -118,8 +118,10 @@ int launch_exclusive_scan_u64(const unsigned long long *in, unsigned long long *
                               unsigned long long *total, bool append_total, int num_sms, cudaStream_t st);
 
 // SHUFFLE (multi-GPU)
-// Part layout: 32-byte header {n_short, long_bytes, 0, 0}, n_short records of 32 bytes
-// {k0, k1, count, 0}, then long records {len, count, key bytes padded to 16}.
+// Part layout: 32-byte header {n_short, long_bytes, long_off, 0}, n_short records of 32 bytes
+// {k0, k1, count, 0} from byte 32, long records {len, count, key bytes padded to 16} from
+// byte long_off (right behind the short records when packed for NCCL, at a fixed offset
+// when packed straight into a peer's slot).
 // part_counts: 2 * nparts scalars (short records, long bytes per part).
 int launch_shuffle_count(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
                          const Counters *ctr, uint32_t nparts, unsigned long long *part_counts, int num_sms,
@@ -129,6 +131,12 @@ int launch_shuffle_pack(const Slot *table, uint64_t slots, const LongOcc *long_l
                         const Counters *ctr, uint32_t nparts, uint8_t *out, const unsigned long long *part_offsets,
                         const unsigned long long *part_counts, unsigned long long *part_cursors, int num_sms,
                         cudaStream_t st);
+// pack + send in one kernel: part q goes to dev_dst[q] (a slot in a peer's receive buffer);
+// part_cursors: 2 * nparts scalars, zeroed by the caller; *xflag |= 1 when something did not fit
+int launch_shuffle_pack_peers(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
+                              const Counters *ctr, uint32_t nparts, uint8_t *const *dev_dst, uint64_t short_cap,
+                              uint64_t long_room, unsigned long long *part_cursors, uint32_t *xflag, int num_sms,
+                              cudaStream_t st);
 // adds one received part to the table / long list of p
 int launch_shuffle_merge(const uint8_t *part, uint64_t nbytes, MapParams p, int num_sms, cudaStream_t st);
 

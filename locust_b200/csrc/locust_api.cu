@@ -19,6 +19,12 @@ struct Segment {
     const uint8_t *dev;   // device bytes
     uint64_t nbytes;
     uint8_t *owned;       // non-null when the context made the device copy
+    uint64_t owned_cap;   // size of that allocation
+};
+
+struct Spare {            // a device copy of an earlier job, kept for the next one
+    uint8_t *ptr;
+    uint64_t cap;
 };
 
 constexpr uint64_t kHostChunk = 32ull << 20;   // host->device copy granularity
@@ -46,6 +52,7 @@ struct locust_ctx {
     uint32_t epoch = 1;
 
     std::vector<Segment> segments;
+    std::vector<Spare> spares;      // cudaMalloc / cudaFree per job is slow, more so with peer mappings open
     bool cleared = false;           // table/counters zeroed for the current job
     bool shuffled = false;          // partials were packed; the table now holds merged records
     bool replayable = true;         // the job can be redone from `segments` alone (false once records were merged in)
@@ -63,6 +70,9 @@ struct locust_ctx {
     unsigned long long *part_dev = nullptr;  uint32_t part_cap = 0;
     std::vector<unsigned long long> part_host, part_off_host;
     uint32_t part_n = 0;
+    // direct exchange: overflow flag of pack_peers (device + pinned mirror), receive buffers we own
+    uint32_t *xflag = nullptr, *h_xflag = nullptr;
+    std::vector<void *> exchange_bufs;
 
     cudaEvent_t ev[8]{};            // map, process, reduce, shuffle: begin/end
     bool ev_set[8]{};
@@ -139,6 +149,7 @@ uint32_t take_epochs(locust_ctx *c, uint32_t k) {
 int clear_job(locust_ctx *c) {
     CU(cudaMemsetAsync(c->table, 0, c->slots * sizeof(Slot), c->stream));
     CU(cudaMemsetAsync(c->ctr, 0, sizeof(Counters), c->stream));
+    CU(cudaMemsetAsync(c->xflag, 0, sizeof(uint32_t), c->stream));
     c->cleared = true;
     c->shuffled = false;
     c->stage = 0;
@@ -147,8 +158,26 @@ int clear_job(locust_ctx *c) {
 }
 
 void drop_segments(locust_ctx *c) {
-    for (auto &s : c->segments) cudaFree(s.owned);
+    for (auto &s : c->segments) {
+        if (!s.owned) continue;
+        if (c->spares.size() < 4) c->spares.push_back(Spare{s.owned, s.owned_cap});
+        else cudaFree(s.owned);
+    }
     c->segments.clear();
+}
+
+// device memory for a copy of `nbytes` input bytes: a spare of an earlier job if one is large enough
+cudaError_t take_device_copy(locust_ctx *c, uint64_t nbytes, uint8_t **dev, uint64_t *cap) {
+    for (size_t i = 0; i < c->spares.size(); ++i) {
+        if (c->spares[i].cap >= nbytes) {
+            *dev = c->spares[i].ptr; *cap = c->spares[i].cap;
+            c->spares.erase(c->spares.begin() + (long)i);
+            return cudaSuccess;
+        }
+    }
+    if (c->spares.size() >= 4) { cudaFree(c->spares.front().ptr); c->spares.erase(c->spares.begin()); }
+    *cap = nbytes;
+    return cudaMalloc(reinterpret_cast<void **>(dev), nbytes);
 }
 
 MapParams map_params(locust_ctx *c, const uint8_t *dev, uint64_t lo_abs, uint64_t hi_abs) {
@@ -232,6 +261,7 @@ int run_reduce_async(locust_ctx *c) {
     CU(cudaGetLastError());
     CU(cudaEventRecord(c->ev[5], c->stream)); c->ev_set[5] = true;
     CU(cudaMemcpyAsync(c->h_ctr, c->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(c->h_xflag, c->xflag, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
     return LOCUST_OK;
 }
 
@@ -272,6 +302,12 @@ int finish_reduce(locust_ctx *c) {
         int rc = run_reduce_async(c);
         if (rc) return rc;
         CU(cudaStreamSynchronize(c->stream));
+        if (*c->h_xflag & 2u)
+            return fail(c, LOCUST_E_CAPACITY, "MAP overflowed the combiner table or the long-token list before "
+                                              "locust_shuffle_pack_peers (raise table_log2 / long_capacity)");
+        if (*c->h_xflag)
+            return fail(c, LOCUST_E_CAPACITY, "locust_shuffle_pack_peers: records did not fit the destination slot "
+                                              "(raise slot_bytes); the job's result is incomplete");
         const uint32_t st = c->h_ctr->status;
         if (!(st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull | kStatusBlobFull))) {
             c->stage = 2;
@@ -353,6 +389,9 @@ int locust_create(const locust_config *cfg, locust_ctx **out) {
     for (auto &ev : c->ev) CU(cudaEventCreate(&ev));
     CU(map_kernel_setup());
     CU(dalloc(&c->ctr, 1));
+    CU(dalloc(&c->xflag, 1));
+    CU(cudaMallocHost(reinterpret_cast<void **>(&c->h_xflag), sizeof(uint32_t)));
+    *c->h_xflag = 0;
     CU(cudaMallocHost(reinterpret_cast<void **>(&c->h_ctr), sizeof(Counters)));
     memset(c->h_ctr, 0, sizeof(Counters));
     CU(dalloc(&c->sort.hist, 16 * 256));
@@ -372,10 +411,13 @@ int locust_destroy(locust_ctx *c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     drop_segments(c);
+    for (auto &sp : c->spares) cudaFree(sp.ptr);
     cudaFree(c->table); cudaFree(c->long_list); cudaFree(c->ctr);
     free_record_buffers(c);
     cudaFree(c->sort.hist); cudaFree(c->sort.bases); cudaFree(c->sort.tickets);
-    cudaFree(c->line_off); cudaFree(c->d_text); cudaFree(c->part_dev);
+    cudaFree(c->line_off); cudaFree(c->d_text); cudaFree(c->part_dev); cudaFree(c->xflag);
+    for (void *b : c->exchange_bufs) cudaFree(b);
+    cudaFreeHost(c->h_xflag);
     cudaFreeHost(c->h_ctr); cudaFreeHost(c->h_blob); cudaFreeHost(c->h_offsets);
     cudaFreeHost(c->h_counts); cudaFreeHost(c->h_vals); cudaFreeHost(c->h_text);
     for (auto &ev : c->ev) if (ev) cudaEventDestroy(ev);
@@ -416,13 +458,14 @@ int locust_map(locust_ctx *c, const void *data, uint64_t nbytes, int where) {
     int rc = LOCUST_OK;
     if (nbytes) {
         if (where == LOCUST_DEVICE) {
-            Segment s{static_cast<const uint8_t *>(data), nbytes, nullptr};
+            Segment s{static_cast<const uint8_t *>(data), nbytes, nullptr, 0};
             c->segments.push_back(s);
             rc = run_map_segment(c, s);
         } else {
             uint8_t *dev = nullptr;
-            CU(cudaMalloc(reinterpret_cast<void **>(&dev), nbytes + 64));
-            c->segments.push_back(Segment{dev, nbytes, dev});
+            uint64_t cap = 0;
+            CU(take_device_copy(c, nbytes + 64, &dev, &cap));
+            c->segments.push_back(Segment{dev, nbytes, dev, cap});
             rc = map_host(c, static_cast<const uint8_t *>(data), nbytes, dev);
         }
     }
@@ -584,13 +627,14 @@ int locust_map_intermediate(locust_ctx *c, const char *text, uint64_t nbytes) {
     }
     const uint64_t n_short = shorts.size() / 4, total = (32 + 32 * n_short + longs.size() + 31) & ~31ull;
     std::vector<uint8_t> part(total, 0);
-    const uint64_t hdr[4] = {n_short, (uint64_t)longs.size(), 0, 0};
+    const uint64_t hdr[4] = {n_short, (uint64_t)longs.size(), 32 + 32 * n_short, 0};
     memcpy(part.data(), hdr, 32);
     if (n_short) memcpy(part.data() + 32, shorts.data(), 32 * n_short);
     if (!longs.empty()) memcpy(part.data() + 32 + 32 * n_short, longs.data(), longs.size());
     uint8_t *dev = nullptr;
-    CU(cudaMalloc(reinterpret_cast<void **>(&dev), total));
-    c->segments.push_back(Segment{dev, 0, dev});           // owned: long keys point into it until reset
+    uint64_t cap = 0;
+    CU(take_device_copy(c, total, &dev, &cap));
+    c->segments.push_back(Segment{dev, 0, dev, cap});      // owned: long keys point into it until reset
     CU(cudaMemcpyAsync(dev, part.data(), total, cudaMemcpyHostToDevice, c->stream));
     MapParams p = map_params(c, dev, 0, 0);
     c->launches += (uint64_t)launch_shuffle_merge(dev, total, p, c->num_sms, c->stream);
@@ -660,6 +704,82 @@ int locust_shuffle_pack(locust_ctx *c, uint32_t nparts, void *dev_out, const uin
                                                  c->part_dev + 2ull * nparts, c->num_sms, c->stream);
     CU(cudaGetLastError());
     return LOCUST_OK;      // (the offsets came from pageable memory: that copy was staged before it returned)
+}
+
+int locust_exchange_alloc(locust_ctx *c, uint64_t nbytes, void **dev_buf) {
+    if (!c || !dev_buf || nbytes == 0) return LOCUST_E_ARG;
+    CU(cudaSetDevice(c->device));
+    void *b = nullptr;
+    CU(cudaMalloc(&b, nbytes));
+    CU(cudaMemsetAsync(b, 0, nbytes, c->stream));          // empty headers: a slot nobody wrote merges as nothing
+    CU(cudaStreamSynchronize(c->stream));
+    c->exchange_bufs.push_back(b);
+    *dev_buf = b;
+    return LOCUST_OK;
+}
+
+int locust_ipc_export(locust_ctx *c, const void *dev_buf, uint8_t handle[64]) {
+    if (!c || !dev_buf || !handle) return LOCUST_E_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    CU(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, const_cast<void *>(dev_buf)));
+    memcpy(handle, &h, 64);
+    return LOCUST_OK;
+}
+
+int locust_ipc_open(locust_ctx *c, const uint8_t handle[64], void **dev_buf) {
+    if (!c || !handle || !dev_buf) return LOCUST_E_ARG;
+    CU(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    CU(cudaIpcOpenMemHandle(dev_buf, h, cudaIpcMemLazyEnablePeerAccess));
+    return LOCUST_OK;
+}
+
+int locust_ipc_close(locust_ctx *c, void *dev_buf) {
+    if (!c || !dev_buf) return LOCUST_E_ARG;
+    CU(cudaSetDevice(c->device));
+    CU(cudaIpcCloseMemHandle(dev_buf));
+    return LOCUST_OK;
+}
+
+int locust_shuffle_pack_peers(locust_ctx *c, uint32_t nparts, void *const *dst_slots, uint64_t slot_bytes,
+                              uint64_t short_cap) {
+    if (!c || !dst_slots || nparts == 0) return LOCUST_E_ARG;
+    if (nparts > 256) return fail(c, LOCUST_E_ARG, "locust_shuffle_pack_peers: at most 256 parts");
+    if (slot_bytes % 32 || slot_bytes < 32 + 32 * short_cap)
+        return fail(c, LOCUST_E_ARG, "locust_shuffle_pack_peers: slot_bytes must be a multiple of 32 and hold short_cap records");
+    if (c->stage != 0) return fail(c, LOCUST_E_STATE, "locust_shuffle_pack_peers after locust_process");
+    CU(cudaSetDevice(c->device));
+    if (!c->cleared) {
+        CU(cudaEventRecord(c->ev[0], c->stream)); c->ev_set[0] = true;
+        int rc0 = clear_job(c);
+        if (rc0) return rc0;
+        CU(cudaEventRecord(c->ev[1], c->stream)); c->ev_set[1] = true;
+    }
+    if (!c->ev_set[6]) { CU(cudaEventRecord(c->ev[6], c->stream)); c->ev_set[6] = true; }
+    if (nparts > c->part_cap) {
+        cudaFree(c->part_dev); c->part_dev = nullptr;
+        c->part_cap = nparts;
+        CU(dalloc(&c->part_dev, 5ull * nparts));
+    }
+    // device copy of the destination pointers lives behind the cursors (same layout as the offsets of the NCCL path)
+    c->part_off_host.resize(nparts);
+    for (uint32_t i = 0; i < nparts; ++i) {
+        if (!dst_slots[i]) return fail(c, LOCUST_E_ARG, "locust_shuffle_pack_peers: NULL destination");
+        c->part_off_host[i] = reinterpret_cast<unsigned long long>(dst_slots[i]);
+    }
+    CU(cudaMemsetAsync(c->part_dev, 0, 4ull * nparts * sizeof(unsigned long long), c->stream));
+    CU(cudaMemcpyAsync(c->part_dev + 4ull * nparts, c->part_off_host.data(), nparts * sizeof(unsigned long long),
+                       cudaMemcpyHostToDevice, c->stream));
+    c->launches += (uint64_t)launch_shuffle_pack_peers(
+        c->table, c->slots, c->long_list, c->long_cap, c->ctr, nparts,
+        reinterpret_cast<uint8_t *const *>(c->part_dev + 4ull * nparts), short_cap, slot_bytes - 32 - 32 * short_cap,
+        c->part_dev + 2ull * nparts, c->xflag, c->num_sms, c->stream);
+    CU(cudaGetLastError());
+    c->replayable = false;      // a MAP overflow can no longer be repaired by redoing MAP: the parts are gone
+    return LOCUST_OK;
 }
 
 int locust_shuffle_begin_merge(locust_ctx *c) {

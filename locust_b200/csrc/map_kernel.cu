@@ -341,15 +341,15 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
 }
 
 // ---- merge side of the shuffle (loadIntermediateFile's role, main.cu:66-103) ---------
-// One received part: header {n_short, long_bytes}, short records {k0, k1, count, 0},
-// long records {len, count, bytes padded to 16}.  Short records go through the same
+// One received part: header {n_short, long_bytes, long_off, 0}, short records {k0, k1,
+// count, 0} from byte 32, long records {len, count, bytes padded to 16} from byte long_off.  Short records go through the same
 // table insert as MAP; long records are appended to the long-token list, pointing
 // into the received buffer.
 __global__ void __launch_bounds__(256) shuffle_merge_kernel(const uint8_t *__restrict__ part, uint64_t nbytes,
                                                             const __grid_constant__ MapParams p) {
     const unsigned long long *hdr = reinterpret_cast<const unsigned long long *>(part);
-    const unsigned long long n_short = hdr[0], long_bytes = hdr[1];
-    if (32ull + 32ull * n_short + long_bytes > nbytes) {            // malformed part: refuse loudly
+    const unsigned long long n_short = hdr[0], long_bytes = hdr[1], long_off = hdr[2];
+    if (32ull + 32ull * n_short > long_off || long_off + long_bytes > nbytes) {     // malformed part: refuse loudly
         if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(&p.ctr->status, kStatusEntryFull);
         return;
     }
@@ -360,7 +360,7 @@ __global__ void __launch_bounds__(256) shuffle_merge_kernel(const uint8_t *__res
         global_insert(p, v.x, v.y, v.z);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {                      // long records are rare: one thread walks them
-        const uint8_t *q = part + 32ull + 32ull * n_short;
+        const uint8_t *q = part + long_off;
         unsigned long long done = 0;
         while (done < long_bytes) {
             const unsigned long long len = reinterpret_cast<const unsigned long long *>(q + done)[0];

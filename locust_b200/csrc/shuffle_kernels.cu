@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(256) shuffle_pack_kernel(const Slot *__restric
     const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (tid < nparts) {       // headers
         unsigned long long *h = reinterpret_cast<unsigned long long *>(out + part_offsets[tid]);
-        h[0] = part_counts[tid]; h[1] = part_counts[nparts + tid]; h[2] = 0ull; h[3] = 0ull;
+        h[0] = part_counts[tid]; h[1] = part_counts[nparts + tid]; h[2] = 32ull + 32ull * part_counts[tid]; h[3] = 0ull;
     }
     // short records: every round the block reserves its records' places per part with one atomic
     const uint64_t rounds = (slots + stride - 1) / stride;
@@ -98,6 +98,79 @@ __global__ void __launch_bounds__(256) shuffle_pack_kernel(const Slot *__restric
     }
 }
 
+// ---- pack + send in one kernel ------------------------------------------------------------
+// Each part is written straight into its destination: dst[p] is this rank's slot inside
+// rank p's receive buffer, a peer-mapped address (NVLink) unless p is this rank.  No sizes are
+// exchanged beforehand: a slot has room for `short_cap` short records at byte 32 and for
+// `long_room` bytes of long records at byte 32 + 32 * short_cap, and its header (written last,
+// by shuffle_headers_kernel) says how much of each arrived.  What does not fit is dropped and
+// flagged in *xflag; short_cap = the sender's table size can never overflow.
+__global__ void __launch_bounds__(256) shuffle_pack_peers_kernel(const Slot *__restrict__ table, uint64_t slots,
+                                                                 const LongOcc *__restrict__ long_list,
+                                                                 uint64_t long_cap, const Counters *ctr,
+                                                                 uint32_t nparts, uint8_t *const *__restrict__ dst,
+                                                                 uint64_t short_cap, uint64_t long_room,
+                                                                 unsigned long long *part_cursors, uint32_t *xflag) {
+    __shared__ unsigned long long sh_cnt[kMaxParts], sh_base[kMaxParts];
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t rounds = (slots + stride - 1) / stride;
+    for (uint64_t r = 0; r < rounds; ++r) {
+        for (uint32_t i = threadIdx.x; i < nparts; i += blockDim.x) sh_cnt[i] = 0ull;
+        __syncthreads();
+        const uint64_t i = r * stride + tid;
+        ulonglong4 v = make_ulonglong4(0ull, 0ull, 0ull, 0ull);
+        if (i < slots) v = *reinterpret_cast<const ulonglong4 *>(table + i);
+        const bool occ = (v.x | v.y) != 0ull;
+        uint32_t part = 0;
+        unsigned long long local = 0;
+        if (occ) { part = part_of_short(v.x, v.y, nparts); local = atomicAdd(&sh_cnt[part], 1ull); }
+        __syncthreads();
+        for (uint32_t q = threadIdx.x; q < nparts; q += blockDim.x)
+            sh_base[q] = sh_cnt[q] ? atomicAdd(&part_cursors[q], sh_cnt[q]) : 0ull;
+        __syncthreads();
+        if (occ) {
+            const unsigned long long at = sh_base[part] + local;
+            if (at < short_cap) reinterpret_cast<ulonglong4 *>(dst[part] + 32)[at] = make_ulonglong4(v.x, v.y, v.z, 0ull);
+            else atomicOr(xflag, 1u);
+        }
+        __syncthreads();
+    }
+    unsigned long long nl = ctr->n_long;
+    if (nl > long_cap) nl = long_cap;
+    for (uint64_t i = tid; i < nl; i += stride) {
+        const LongOcc t = long_list[i];
+        const uint32_t part = part_of_long(t.ptr, t.len, nparts);
+        const uint64_t need = long_record_bytes(t.len);
+        const unsigned long long at = atomicAdd(&part_cursors[nparts + part], need);
+        if (at + need > long_room) { atomicOr(xflag, 1u); continue; }
+        uint8_t *d = dst[part] + 32ull + 32ull * short_cap + at;
+        reinterpret_cast<unsigned long long *>(d)[0] = t.len;
+        reinterpret_cast<unsigned long long *>(d)[1] = t.count;
+        const uint64_t padded = (t.len + 15ull) & ~15ull;
+        for (uint64_t b = 0; b < padded; ++b) d[16 + b] = b < t.len ? t.ptr[b] : (uint8_t)0;
+    }
+    __threadfence_system();          // the records have to be in the peer's memory before the header says so
+}
+
+// Long records that overflowed were dropped one by one, so the long area may have holes past
+// the first drop: report only what is certainly contiguous (everything, when nothing overflowed;
+// nothing, when something did -- the job fails on the flag anyway).
+__global__ void shuffle_headers_kernel(uint32_t nparts, uint8_t *const *__restrict__ dst, uint64_t short_cap,
+                                       uint64_t long_room, const unsigned long long *part_cursors,
+                                       const Counters *ctr, uint32_t *xflag) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= nparts) return;
+    // the counters are about to be cleared for the merge: keep MAP's overflow bits where REDUCE looks
+    if (p == 0 && (ctr->status & (kStatusTableFull | kStatusLongFull))) atomicOr(xflag, 2u);
+    unsigned long long ns = part_cursors[p], lb = part_cursors[nparts + p];
+    if (ns > short_cap) ns = short_cap;
+    if (lb > long_room) lb = 0ull;
+    unsigned long long *h = reinterpret_cast<unsigned long long *>(dst[p]);
+    h[0] = ns; h[1] = lb; h[2] = 32ull + 32ull * short_cap; h[3] = 0ull;
+    __threadfence_system();
+}
+
 static inline unsigned grid_for(uint64_t n, int num_sms) {
     uint64_t g = (n + 1023) / 1024;
     const uint64_t cap = (uint64_t)num_sms * 8;
@@ -121,6 +194,16 @@ int launch_shuffle_pack(const Slot *table, uint64_t slots, const LongOcc *long_l
     shuffle_pack_kernel<<<grid_for(slots, num_sms), 256, 0, st>>>(table, slots, long_list, long_cap, ctr, nparts, out,
                                                                  part_offsets, part_counts, part_cursors);
     return 1;
+}
+
+int launch_shuffle_pack_peers(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
+                              const Counters *ctr, uint32_t nparts, uint8_t *const *dev_dst, uint64_t short_cap,
+                              uint64_t long_room, unsigned long long *part_cursors, uint32_t *xflag, int num_sms,
+                              cudaStream_t st) {
+    shuffle_pack_peers_kernel<<<grid_for(slots, num_sms), 256, 0, st>>>(table, slots, long_list, long_cap, ctr, nparts,
+                                                                       dev_dst, short_cap, long_room, part_cursors, xflag);
+    shuffle_headers_kernel<<<(nparts + 255) / 256, 256, 0, st>>>(nparts, dev_dst, short_cap, long_room, part_cursors, ctr, xflag);
+    return 2;
 }
 
 }  // namespace locust

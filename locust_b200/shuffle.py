@@ -8,6 +8,8 @@ command channel (Distributor/slave.py) -- with an all-to-all over NVLink:
     map (each rank, its shard)            locust_map
     pack partials by destination          locust_shuffle_sizes / locust_shuffle_pack
     all-to-all of sizes, then of records  torch.distributed (NCCL; gloo in the CPU tests)
+      -- or, on one box, both at once:    locust_shuffle_pack_peers writes every part straight
+                                          into the destination GPU's memory over NVLink (PeerExchange)
     merge what arrived                    locust_shuffle_begin_merge / locust_shuffle_merge
     gather the partitions on rank 0       the same pack / exchange / merge with one destination
     process + reduce on rank 0            locust_process / locust_reduce  -> sorted result
@@ -73,12 +75,58 @@ class GpuBackend:
         self.wc.reduce()
 
 
+class PeerExchange:
+    """Receive buffers for the fused pack + send path, mapped into every rank of one box.
+
+    Rank r owns two buffers of `world` slots each (hash shuffle, gather); slot s of a buffer is
+    where rank s writes.  The buffers are cudaMalloc'ed by liblocust, their IPC handles are
+    all-gathered once, and every rank maps every other rank's buffers (NVLink peer access).  A
+    slot holds `short_cap` short records plus `long_room` bytes of long records; short_cap is the
+    sender's table size, so short records can never overflow."""
+
+    def __init__(self, wc, dist, device, table_slots, long_room=16 << 20, group=None):
+        import torch
+        self.wc, self.dist, self.group = wc, dist, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.short_cap = int(table_slots)
+        self.slot_bytes = 32 + 32 * self.short_cap + int(long_room)
+        self.slot_bytes = (self.slot_bytes + 31) // 32 * 32
+        # only rank 0 receives the gather; everyone receives the hash shuffle
+        self.mine = [wc.exchange_alloc(self.slot_bytes * self.world),
+                     wc.exchange_alloc(self.slot_bytes * (self.world if self.rank == 0 else 1))]
+        handles = torch.tensor(list(wc.ipc_export(self.mine[0]) + wc.ipc_export(self.mine[1])),
+                               dtype=torch.uint8, device=device)
+        allh = torch.empty(self.world * 128, dtype=torch.uint8, device=device)
+        dist.all_gather_into_tensor(allh, handles, group=group)
+        allh = bytes(allh.cpu().numpy())
+        self.bufs = []            # bufs[r] = (shuffle buffer of rank r, gather buffer of rank r), as seen from here
+        for r in range(self.world):
+            if r == self.rank:
+                self.bufs.append((self.mine[0], self.mine[1]))
+            else:
+                h = allh[r * 128:(r + 1) * 128]
+                self.bufs.append((wc.ipc_open(h[:64]), wc.ipc_open(h[64:])))
+        self._token = torch.zeros(1, dtype=torch.int32, device=device)
+
+    def barrier(self):
+        """every rank's packing kernel has finished before any rank merges: a one-element
+        all-reduce on the current stream (no host synchronisation)"""
+        self.dist.all_reduce(self._token, group=self.group)
+
+    def close(self):
+        for r, (a, b) in enumerate(self.bufs):
+            if r != self.rank:
+                self.wc.ipc_close(a)
+                self.wc.ipc_close(b)
+        self.bufs = []
+
+
 class DistributedWordCount:
     """run(shard) on every rank; afterwards rank 0's backend holds the sorted result of the
     whole input and the other ranks hold an empty one."""
 
-    def __init__(self, backend, dist, group=None):
-        self.b, self.dist, self.group = backend, dist, group
+    def __init__(self, backend, dist, group=None, peers=None):
+        self.b, self.dist, self.group, self.peers = backend, dist, group, peers
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
         self.last_shuffle_bytes = 0          # bytes this rank sent to other ranks in the hash shuffle
@@ -116,11 +164,26 @@ class DistributedWordCount:
             off += s
         return send_sizes
 
+    def _shuffle_peers(self, which, dests):
+        """fused path: part i is written by the packing kernel into rank dests[i]'s buffer
+        `which` (0 hash shuffle, 1 gather), slot = my rank; barrier; merge my own slots"""
+        px, wc = self.peers, self.b.wc
+        dst = [px.bufs[d][which] + self.rank * px.slot_bytes for d in dests]
+        wc.shuffle_pack_peers(dst, px.slot_bytes, px.short_cap)
+        px.barrier()
+        wc.shuffle_begin_merge()
+        nslots = self.world if (which == 0 or self.rank == 0) else 0
+        for s in range(nslots):
+            wc.shuffle_merge(px.mine[which] + s * px.slot_bytes, px.slot_bytes)
+
     def run(self, shard):
         b = self.b
         b.reset()
         b.map(shard)
-        if self.world > 1:
+        if self.world > 1 and self.peers is not None:
+            self._shuffle_peers(0, list(range(self.world)))
+            self._shuffle_peers(1, [0])
+        elif self.world > 1:
             # hash-partitioned exchange: part i goes to rank i
             sent = self._shuffle(self.world, list(range(self.world)))
             self.last_shuffle_bytes = sum(s for r, s in enumerate(sent) if r != self.rank)

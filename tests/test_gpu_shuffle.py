@@ -99,7 +99,8 @@ def test_hash_partitions_are_disjoint_and_balanced(lb):
     import struct
     seen, total = {}, 0
     for p_, (o, x) in enumerate(zip(offs, sizes)):
-        n_short, long_bytes, _, _ = struct.unpack_from("<4Q", raw, o)
+        n_short, long_bytes, long_off, _ = struct.unpack_from("<4Q", raw, o)
+        assert long_off == 32 + 32 * n_short
         assert (32 + 32 * n_short + long_bytes + 31) // 32 * 32 == x
         q = o + 32
         for _ in range(n_short):
@@ -134,3 +135,61 @@ def test_synthetic_c3_style_two_ranks(lb):
     keys, counts, _ = emulate(lb, host, 2, table_log2=19)
     ref = pyoracle.wordcount(host, mode="fast", formats=False)
     assert keys == ref.keys and counts == ref.counts
+
+
+@pytest.mark.parametrize("P", [2, 5])
+def test_pack_straight_into_peer_slots(lb, P):
+    """locust_shuffle_pack_peers: the packing kernel writes every part into the destination
+    rank's receive buffer itself (on a multi-GPU box those are NVLink peer addresses; here the
+    ranks are contexts on one GPU, so no IPC mapping is needed).  Two jobs in a row: the
+    slots of the first job must not leak into the second."""
+    from oracle import pyoracle
+    texts = [golden_input("hamlet") + golden_input("edge_long_tokens") + b" " + golden_input("rand_longtok_s5"),
+             golden_input("rand_heavy_s4")]
+    log2 = 14
+    short_cap = 1 << log2
+    slot_bytes = 32 + 32 * short_cap + (1 << 20)
+    ctx = [lb.WordCount(device=0, table_log2=log2) for _ in range(P)]
+    shuffle_buf = [c.exchange_alloc(slot_bytes * P) for c in ctx]
+    gather_buf = ctx[0].exchange_alloc(slot_bytes * P)
+    try:
+        for data in texts:
+            dev = torch.frombuffer(bytearray(data), dtype=torch.uint8).cuda()
+            for r, (lo, hi) in enumerate(plan_shards(data, P)):
+                ctx[r].reset()
+                ctx[r].map(dev[lo:hi])
+            for r in range(P):                                    # hash shuffle: part p -> rank p, slot r
+                ctx[r].shuffle_pack_peers([shuffle_buf[p] + r * slot_bytes for p in range(P)], slot_bytes, short_cap)
+            torch.cuda.synchronize()                              # stands in for the barrier over all ranks
+            for r in range(P):
+                ctx[r].shuffle_begin_merge()
+                for s in range(P):
+                    ctx[r].shuffle_merge(shuffle_buf[r] + s * slot_bytes, slot_bytes)
+            for r in range(P):                                    # gather on rank 0
+                ctx[r].shuffle_pack_peers([gather_buf + r * slot_bytes], slot_bytes, short_cap)
+            torch.cuda.synchronize()
+            for r in range(P):
+                ctx[r].shuffle_begin_merge()
+            for s in range(P):
+                ctx[0].shuffle_merge(gather_buf + s * slot_bytes, slot_bytes)
+            for r in range(P):
+                ctx[r].process()
+                ctx[r].reduce()
+            keys, counts, _ = ctx[0].result()
+            ref = pyoracle.wordcount(data)
+            assert keys == ref.keys and counts == ref.counts
+            assert all(ctx[r].stats()["unique_keys"] == 0 for r in range(1, P))
+        # a slot that is too small for the long records is reported, not silently truncated
+        tiny = 32 + 32 * short_cap + 64
+        ctx[0].reset()
+        ctx[0].map(torch.frombuffer(bytearray(texts[0]), dtype=torch.uint8).cuda())
+        small = ctx[0].exchange_alloc(tiny)
+        ctx[0].shuffle_pack_peers([small], tiny, short_cap)
+        ctx[0].shuffle_begin_merge()
+        ctx[0].shuffle_merge(small, tiny)
+        ctx[0].process()
+        with pytest.raises(lb.LocustError, match="did not fit"):
+            ctx[0].reduce()
+    finally:
+        for c in ctx:
+            c.close()

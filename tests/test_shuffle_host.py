@@ -71,7 +71,7 @@ class PyBackend:
     def shuffle_pack(self, nparts, out, offsets):
         view = out.numpy()
         for (shorts, longs), off in zip(self._packed, offsets):
-            blob = struct.pack("<4Q", len(shorts), self._long_bytes(longs), 0, 0)
+            blob = struct.pack("<4Q", len(shorts), self._long_bytes(longs), 32 + 32 * len(shorts), 0)
             for k, c in shorts:
                 blob += k.ljust(16, b"\0") + struct.pack("<2Q", c, 0)
             for k, c in longs:
@@ -83,14 +83,15 @@ class PyBackend:
 
     def merge(self, buf, offset, nbytes):
         raw = bytes(buf.numpy()[offset:offset + nbytes])
-        n_short, long_bytes, _, _ = struct.unpack_from("<4Q", raw, 0)
-        assert 32 + 32 * n_short + long_bytes <= nbytes
+        n_short, long_bytes, long_off, _ = struct.unpack_from("<4Q", raw, 0)
+        assert 32 + 32 * n_short <= long_off and long_off + long_bytes <= nbytes
         p = 32
         for _ in range(n_short):
             k = raw[p:p + 16].rstrip(b"\0")
             c = struct.unpack_from("<Q", raw, p + 16)[0]
             self.counts[k] = self.counts.get(k, 0) + c
             p += 32
+        p = long_off
         end = p + long_bytes
         while p < end:
             ln, c = struct.unpack_from("<2Q", raw, p)

@@ -1,0 +1,43 @@
+#!/usr/bin/env python
+"""Run under torchrun on >= 2 GPUs: the fused pack+send path (IPC-mapped peer buffers, NVLink)
+and the NCCL all-to-all path must both give the oracle's result on rank 0."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch, torch.distributed as dist
+import locust_b200
+from locust_b200.textgen import TextGen
+from locust_b200.shuffle import DistributedWordCount, GpuBackend, PeerExchange
+
+rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(lr); dev = torch.device("cuda", lr)
+dist.init_process_group("nccl", device_id=dev)
+per = 32 << 20
+g = TextGen.config("C3", total_bytes=per * world, device=lr, vocab=300000)
+text = torch.empty(per, dtype=torch.uint8, device=dev); g.fill_device(text, byte_offset=rank * per); torch.cuda.synchronize()
+# a few long tokens so the long-record area is exercised too
+extra = ("\n" + " ".join("longtoken%02d%s" % (i % 7, "x" * (20 + i % 5)) for i in range(50 * (rank + 1))) + "\n").encode()
+text = torch.cat([text, torch.frombuffer(bytearray(extra), dtype=torch.uint8).to(dev)])
+st = torch.cuda.Stream(device=dev)
+log2 = 20
+wc = locust_b200.WordCount(device=lr, table_log2=log2, stream=st.cuda_stream)
+results = {}
+with torch.cuda.stream(st):
+    px = PeerExchange(wc, dist, dev, 1 << log2)
+    for name, peers in (("nccl", None), ("peers", px), ("peers again", px)):
+        job = DistributedWordCount(GpuBackend(wc, dev), dist, peers=peers)
+        job.run(text)
+        results[name] = wc.result()[:2]
+    px.close()
+gathered = [None] * world
+dist.all_gather_object(gathered, bytes(text.cpu().numpy()))
+if rank == 0:
+    from oracle import pyoracle
+    ref = pyoracle.wordcount(b"".join(gathered), mode="fast", formats=False)
+    for name, (keys, counts) in results.items():
+        assert keys == ref.keys and counts == ref.counts, name
+        print("%s: %d keys match the oracle" % (name, len(keys)))
+else:
+    for name, (keys, counts) in results.items():
+        assert keys == [] and counts == []
+dist.destroy_process_group()
+print("rank %d ok" % rank)
