@@ -182,8 +182,21 @@ def main():
     wc = locust_b200.WordCount(device=local_rank, table_log2=table_log2, stream=stream.cuda_stream)
     if world > 1:
         from locust_b200.shuffle import DistributedWordCount, GpuBackend, PeerExchange
-        with torch.cuda.stream(stream):
-            peers = PeerExchange(wc, dist, dev, 1 << table_log2) if args.shuffle == "peers" else None
+        peers = None
+        if args.shuffle == "peers":
+            # every rank must end up on the same path: if mapping the peers' buffers fails anywhere
+            # (IPC not permitted in some container set-ups), all ranks fall back to the NCCL exchange
+            ok = torch.ones(1, dtype=torch.int32, device=dev)
+            with torch.cuda.stream(stream):
+                try:
+                    peers = PeerExchange(wc, dist, dev, 1 << table_log2)
+                except Exception as e:                       # noqa: BLE001 - reported, then agreed on below
+                    sys.stderr.write("rank %d: peer exchange unavailable (%s)\n" % (rank, e))
+                    ok.zero_()
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            torch.cuda.synchronize()
+            if int(ok.item()) == 0:
+                peers, args.shuffle = None, "nccl"
         job = DistributedWordCount(GpuBackend(wc, dev), dist, peers=peers)
         step = lambda buf: job.run(buf)
     else:
