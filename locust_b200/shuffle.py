@@ -91,16 +91,22 @@ class PeerExchange:
         self.short_cap = int(table_slots)
         self.slot_bytes = 32 + 32 * self.short_cap + int(long_room)
         self.slot_bytes = (self.slot_bytes + 31) // 32 * 32
-        # only rank 0 receives the gather; everyone receives the hash shuffle
-        self.mine = [wc.exchange_alloc(self.slot_bytes * self.world),
-                     wc.exchange_alloc(self.slot_bytes * (self.world if self.rank == 0 else 1))]
-        handles = torch.tensor(list(wc.ipc_export(self.mine[0]) + wc.ipc_export(self.mine[1])),
-                               dtype=torch.uint8, device=device)
+        # only rank 0 receives the gather; everyone receives the hash shuffle.  A rank that cannot
+        # allocate still takes part in the all-gather (with an empty handle) so nobody hangs.
+        self.mine, self.bufs, raw = [], [], bytes(128)
+        try:
+            self.mine = [wc.exchange_alloc(self.slot_bytes * self.world),
+                         wc.exchange_alloc(self.slot_bytes * (self.world if self.rank == 0 else 1))]
+            raw = wc.ipc_export(self.mine[0]) + wc.ipc_export(self.mine[1])
+        except Exception:                                        # noqa: BLE001 - raised below, on every rank
+            pass
+        handles = torch.tensor(list(raw), dtype=torch.uint8, device=device)
         allh = torch.empty(self.world * 128, dtype=torch.uint8, device=device)
         dist.all_gather_into_tensor(allh, handles, group=group)
         allh = bytes(allh.cpu().numpy())
-        self.bufs = []            # bufs[r] = (shuffle buffer of rank r, gather buffer of rank r), as seen from here
-        for r in range(self.world):
+        if any(allh[r * 128:(r + 1) * 128] == bytes(128) for r in range(self.world)):
+            raise RuntimeError("a rank could not allocate or export its exchange buffers")
+        for r in range(self.world):          # bufs[r] = (shuffle buffer, gather buffer) of rank r, as seen from here
             if r == self.rank:
                 self.bufs.append((self.mine[0], self.mine[1]))
             else:
