@@ -99,6 +99,36 @@ def cpu_port_rate(sample, threads=1):
     return len(sample) / dt / GB, dt, r
 
 
+def c1_reference(wc):
+    """BASELINE config 1: the reference's own CPU branch (oracle/_ref/MapReduce_cpu, verbatim source with
+    GPU_IMPLEMENTATION 0) on hamlet.txt with its own three timers, next to this library on the same file."""
+    ref_bin = os.path.join(ROOT, "oracle", "_ref", "MapReduce_cpu")
+    hamlet = os.path.join(ROOT, "tests", "golden", "hamlet.txt")
+    if not os.path.exists(ref_bin):
+        return {"unavailable": "oracle/_ref/MapReduce_cpu was not built (needs /root/reference at build time)"}
+    best = None
+    for _ in range(3):
+        t0 = time.perf_counter()
+        out = subprocess.run([ref_bin, hamlet], capture_output=True, check=True).stdout
+        wall = time.perf_counter() - t0
+        ns = {}
+        for line in out.split(b"\n")[:8]:
+            for key in (b"CPU mapping", b"CPU sorting", b"CPU reducing"):
+                if line.startswith(key):
+                    ns[key.decode().split()[1]] = int(line.split()[2])
+        tot = sum(ns.values())
+        if best is None or tot < best[0]:
+            best = (tot, ns, wall)
+    with open(hamlet, "rb") as f:
+        data = f.read()
+    wc.run(data)
+    wc.run(data)
+    gpu_ms = sum(wc.stage_ms())
+    return {"input": "hamlet.txt (191734 B)", "reference_cpu_stage_ns": best[1], "reference_cpu_stages_ms": best[0] / 1e6,
+            "reference_cpu_process_wall_s": best[2], "cores": 1, "this_library_stages_ms": gpu_ms,
+            "note": "0.19 MB is a parity case, not a throughput result"}
+
+
 def run_reference(args, rank, world):
     """The reference's CPU implementation of the path (oracle port: oracle/_ref cannot take more than
     5 800 lines), one host thread like the reference, on a bounded sample of the same workload."""
@@ -264,7 +294,7 @@ def main():
         except Exception:
             pass
     roofline = {"bound": "hbm", "kernel": "tokenize_combine_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                "frac": achieved / peak, "frac_of_nominal_8000_gbs": achieved / 8000.0, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "avg_kernel_ms": avg_map_ms,
                 "map_share_of_step": avg_map_ms * args.steps / ms}
 
@@ -316,6 +346,7 @@ def main():
 
     # ---- the reference's CPU algorithm on this box's host cores (rank 0, N=1) -----------------
     cpu = None
+    input_id = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         sample = host[: args.cpu_sample_mib << 20].numpy()
         rate, dt, r = cpu_port_rate(sample)
@@ -323,13 +354,16 @@ def main():
                "sample": "first %d MiB of the same text (%.1f s): map -> comparison sort of every token -> run-length "
                          "reduce, oracle/wordcount_oracle.c, single thread like the reference"
                          % (args.cpu_sample_mib, dt)}
+        cpu["c1_reference"] = c1_reference(wc)
+        import hashlib
+        input_id = hashlib.sha256(host.numpy()).hexdigest()            # identity of the generated input
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic",
                 "config": {"workload": desc, "bytes_per_gpu": per_gpu, "tokens_per_gpu": tokens if world == 1 else None,
-                           "unique_keys": uniq, "table_log2": table_log2,
+                           "unique_keys": uniq, "table_log2": table_log2, "input_sha256": input_id,
                            "l2": "input per step (%d MiB per GPU) is larger than the 126 MB L2" % (per_gpu >> 20)},
                 "roofline": roofline, "shuffle": shuffle, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
                 "gpu_launches": launches_per_step * args.steps, "gpu_launches_per_step": launches_per_step,
