@@ -16,12 +16,6 @@ constexpr uint32_t kStatusEntryFull = 4u;   // candidate-record buffers too smal
 constexpr uint32_t kStatusBlobFull  = 8u;   // key blob too small
 constexpr uint32_t kStatusTextFull  = 16u;  // formatted-text buffer too small
 
-// One occurrence of a token longer than 16 bytes / the full key of a record.
-struct LongTok {
-    const uint8_t *ptr;   // nullptr for keys of <= 16 bytes
-    uint64_t len;
-};
-
 // One entry of the long-token list: `count` occurrences of the key at ptr[0..len).
 // MAP writes one entry per occurrence (count 1); merged shuffle records carry sums.
 struct LongOcc {
@@ -45,14 +39,20 @@ struct Counters {
     uint32_t pass_src[16];          // buffer pass p reads (0 = A, 1 = B)
 };
 
-// Candidate records.  Sort buffers A/B hold (be0, be1, idx): the first 16 key
-// bytes big endian and zero padded (integer order = byte order, prefix first) and
-// the index of the record's payload (count, ref).
+// A candidate record of PROCESS/REDUCE, 32 bytes so that one record is one memory sector:
+// the radix passes scatter whole records, and an 8-byte-per-array layout would turn every
+// scattered record into three or four partly used sectors.
+struct __align__(32) Rec {
+    uint64_t be0, be1;            // first 16 key bytes, big endian, zero padded: integer order = byte order, prefix first
+    unsigned long long count;     // occurrences combined so far
+    uint32_t len;                 // key length in bytes
+    uint32_t lidx;                // keys longer than 16 bytes: entry of the long-token list that holds the bytes
+};
+
+// Double buffer of records for the sort; `longs` is the long-token list Rec::lidx points into.
 struct Records {
-    uint64_t *a0, *a1, *b0, *b1;
-    uint32_t *ia, *ib;
-    unsigned long long *count;   // by payload index
-    LongTok *ref;                // by payload index
+    Rec *a, *b;
+    const LongOcc *longs;
     uint64_t cap;
 };
 

@@ -100,8 +100,7 @@ template <class T>
 cudaError_t dalloc(T **p, uint64_t n) { return cudaMalloc(reinterpret_cast<void **>(p), n * sizeof(T)); }
 
 void free_record_buffers(locust_ctx *c) {
-    cudaFree(c->rec.a0); cudaFree(c->rec.a1); cudaFree(c->rec.b0); cudaFree(c->rec.b1);
-    cudaFree(c->rec.ia); cudaFree(c->rec.ib); cudaFree(c->rec.count); cudaFree(c->rec.ref);
+    cudaFree(c->rec.a); cudaFree(c->rec.b);
     cudaFree(c->sort.lb_state);
     cudaFree(c->red.head); cudaFree(c->red.rank); cudaFree(c->red.csum); cudaFree(c->red.src_pos); cudaFree(c->red.key_offsets);
     cudaFree(c->red.counts); cudaFree(c->red.vals); cudaFree(c->red.key_blob);
@@ -120,10 +119,8 @@ int alloc_sized(locust_ctx *c, uint64_t slots, uint64_t long_cap) {
     const uint64_t cap = slots + long_cap;
     CU(dalloc(&c->table, slots));
     CU(dalloc(&c->long_list, long_cap));
-    CU(dalloc(&c->rec.a0, cap)); CU(dalloc(&c->rec.a1, cap));
-    CU(dalloc(&c->rec.b0, cap)); CU(dalloc(&c->rec.b1, cap));
-    CU(dalloc(&c->rec.ia, cap)); CU(dalloc(&c->rec.ib, cap));
-    CU(dalloc(&c->rec.count, cap)); CU(dalloc(&c->rec.ref, cap));
+    CU(dalloc(&c->rec.a, cap)); CU(dalloc(&c->rec.b, cap));
+    c->rec.longs = c->long_list;
     c->rec.cap = cap;
     c->lb_words = ((cap + kSortTile - 1) / kSortTile) * 256 + 256;
     CU(dalloc(&c->sort.lb_state, c->lb_words));

@@ -56,6 +56,37 @@ LC_D uint64_t lb_lookback(const uint64_t *state, uint32_t tile, uint32_t stride,
     return sum;
 }
 
+// The same walk done by a whole warp over a single column (stride 1): 32 predecessors per round,
+// one per lane; the nearest inclusive word ends the walk.  All 32 lanes call this together and
+// get the sum.  With tens of thousands of tiles in flight a serial walk costs more than the
+// tile's own work.
+LC_D uint64_t lb_lookback_warp(const uint64_t *state, uint32_t tile, uint32_t epoch, uint32_t lane) {
+    uint64_t sum = 0;
+    uint32_t t = tile;
+    while (t > 0) {
+        const bool valid = lane < t;
+        uint64_t x = 0;
+        if (valid) {
+            const uint64_t *p = state + (t - 1u - lane);
+            x = lb_load(p);
+            uint32_t spins = 0;
+            while ((uint32_t)(x >> 56) != epoch || ((x >> 54) & 3ull) == 0ull) {
+                if (++spins > 16) __nanosleep(64);
+                x = lb_load(p);
+            }
+        }
+        const uint32_t incl = __ballot_sync(0xFFFFFFFFu, valid && ((x >> 54) & 3ull) == kLbInclusive);
+        const uint32_t last = incl ? (uint32_t)__ffs((int)incl) - 1u : 31u;      // nearest inclusive predecessor
+        uint64_t v = (valid && lane <= last) ? (x & kLbValueMask) : 0ull;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+        sum += v;
+        if (incl) break;
+        t -= t < 32u ? t : 32u;
+    }
+    return sum;
+}
+
 // Dynamic tile index: blocks take tiles in the order they start running, so a tile
 // only ever waits on tiles that are already resident.  ticket[0] = next tile,
 // ticket[1] = finished blocks; the last block to finish resets both.

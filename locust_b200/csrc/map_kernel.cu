@@ -212,12 +212,11 @@ LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active
         if (has) {
             const unsigned long long e = base + __popc(m & ((1u << wc.lane) - 1u));
             if (e < p.rec.cap) {
-                p.rec.a0[e] = bswap64((uint64_t)a | ((uint64_t)b << 32));
-                p.rec.a1[e] = bswap64((uint64_t)c | ((uint64_t)d << 32));
-                p.rec.ia[e] = (uint32_t)e;
-                p.rec.count[e] = 1ull;
-                p.rec.ref[e].ptr = nullptr;
-                p.rec.ref[e].len = L;
+                Rec rec;
+                rec.be0 = bswap64((uint64_t)a | ((uint64_t)b << 32));
+                rec.be1 = bswap64((uint64_t)c | ((uint64_t)d << 32));
+                rec.count = 1ull; rec.len = L; rec.lidx = 0xFFFFFFFFu;
+                p.rec.a[e] = rec;
             } else {
                 atomicOr(&p.ctr->status, kStatusEntryFull);
             }

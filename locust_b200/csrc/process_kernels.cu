@@ -20,38 +20,58 @@ LC_D uint32_t key_len16(uint64_t k0, uint64_t k1) {
 }
 
 // ---- extract ------------------------------------------------------------------
+// Compaction of the occupied slots.  A block takes 1024 consecutive slots per round (four per
+// thread, all loads in flight together), counts its occupied ones in shared memory and reserves
+// their places with ONE atomic on the global record counter: a warp-level reservation would put
+// millions of atomics on that single address when the table is large (BASELINE config 4).
 __global__ void __launch_bounds__(256) extract_kernel(const Slot *__restrict__ table, uint64_t slots, Records r,
                                                       Counters *ctr) {
-    const uint32_t lane = threadIdx.x & 31u;
-    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    __shared__ uint32_t warp_cnt[8];
+    __shared__ unsigned long long block_base;
+    const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
+    const uint64_t stride = (uint64_t)gridDim.x * 1024u;
     const uint64_t rounds = (slots + stride - 1) / stride;
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    for (uint64_t it = 0; it < rounds; ++it, i += stride) {
-        ulonglong2 k = make_ulonglong2(0ull, 0ull);
-        unsigned long long cnt = 0;
-        if (i < slots) {
-            const ulonglong4 v = *reinterpret_cast<const ulonglong4 *>(table + i);
-            k.x = v.x; k.y = v.y; cnt = v.z;
+    for (uint64_t it = 0; it < rounds; ++it) {
+        const uint64_t first = it * stride + (uint64_t)blockIdx.x * 1024u;
+        ulonglong4 v[4];
+        uint32_t mine = 0, m[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint64_t i = first + j * 256u + threadIdx.x;
+            v[j] = i < slots ? *reinterpret_cast<const ulonglong4 *>(table + i) : make_ulonglong4(0ull, 0ull, 0ull, 0ull);
         }
-        const bool occ = (k.x | k.y) != 0ull;
-        const uint32_t m = __ballot_sync(kFull, occ);
-        if (m == 0u) continue;
-        unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(&ctr->n_entries, (unsigned long long)__popc(m));
-        base = __shfl_sync(kFull, base, 0);
-        if (occ) {
-            const unsigned long long e = base + __popc(m & ((1u << lane) - 1u));
-            if (e < r.cap) {
-                r.a0[e] = bswap64(k.x);
-                r.a1[e] = bswap64(k.y);
-                r.ia[e] = (uint32_t)e;
-                r.count[e] = cnt;
-                r.ref[e].ptr = nullptr;
-                r.ref[e].len = key_len16(k.x, k.y);
-            } else {
-                atomicOr(&ctr->status, kStatusEntryFull);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            m[j] = __ballot_sync(kFull, (v[j].x | v[j].y) != 0ull);
+            mine += (uint32_t)__popc(m[j]);                      // warp-uniform: this warp's occupied slots
+        }
+        if (lane == 0) warp_cnt[w] = mine;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t tot = 0;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) tot += warp_cnt[k];
+            block_base = tot ? atomicAdd(&ctr->n_entries, (unsigned long long)tot) : 0ull;
+        }
+        __syncthreads();
+        unsigned long long e = block_base;
+        for (uint32_t k = 0; k < w; ++k) e += warp_cnt[k];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if ((v[j].x | v[j].y) != 0ull) {
+                const unsigned long long at = e + __popc(m[j] & ((1u << lane) - 1u));
+                if (at < r.cap) {
+                    Rec rec;
+                    rec.be0 = bswap64(v[j].x); rec.be1 = bswap64(v[j].y); rec.count = v[j].z;
+                    rec.len = key_len16(v[j].x, v[j].y); rec.lidx = 0xFFFFFFFFu;
+                    r.a[at] = rec;
+                } else {
+                    atomicOr(&ctr->status, kStatusEntryFull);
+                }
             }
+            e += __popc(m[j]);
         }
+        __syncthreads();
     }
 }
 
@@ -72,10 +92,10 @@ __global__ void __launch_bounds__(256) append_long_kernel(const LongOcc *__restr
             b0 = (b0 << 8) | t.ptr[b];
             b1 = (b1 << 8) | t.ptr[8 + b];
         }
-        r.a0[e] = b0; r.a1[e] = b1; r.ia[e] = (uint32_t)e;
-        r.count[e] = t.count;
-        r.ref[e].ptr = t.ptr;
-        r.ref[e].len = t.len;
+        Rec rec;
+        rec.be0 = b0; rec.be1 = b1; rec.count = t.count;
+        rec.len = t.len > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)t.len; rec.lidx = (uint32_t)i;
+        r.a[e] = rec;
     }
 }
 __global__ void bump_entries_kernel(uint64_t long_cap, uint64_t cap, Counters *ctr) {
@@ -98,9 +118,9 @@ __global__ void __launch_bounds__(256) sort_hist_kernel(Records r, const Counter
     const unsigned long long n = ctr->n_entries;
     for (unsigned long long i = (unsigned long long)blockIdx.x * 256 + threadIdx.x; i < n;
          i += (unsigned long long)gridDim.x * 256) {
-        const uint64_t k0 = r.a0[i], k1 = r.a1[i];
+        const ulonglong2 k = *reinterpret_cast<const ulonglong2 *>(r.a + i);     // be0, be1
 #pragma unroll
-        for (int p = 0; p < 16; ++p) atomicAdd(&sh[p * 256 + digit_of(k0, k1, p)], 1u);
+        for (int p = 0; p < 16; ++p) atomicAdd(&sh[p * 256 + digit_of(k.x, k.y, p)], 1u);
     }
     __syncthreads();
     for (int i = threadIdx.x; i < 16 * 256; i += 256)
@@ -153,10 +173,8 @@ __global__ void __launch_bounds__(256) sort_pass_kernel(Records r, const uint32_
     const unsigned long long n = ctr->n_entries;
     const uint32_t ntiles = (uint32_t)((n + kSortTile - 1) / kSortTile);
     const bool from_b = ctr->pass_src[pass] != 0u;
-    const uint64_t *s0 = from_b ? r.b0 : r.a0, *s1 = from_b ? r.b1 : r.a1;
-    const uint32_t *si = from_b ? r.ib : r.ia;
-    uint64_t *d0 = from_b ? r.a0 : r.b0, *d1 = from_b ? r.a1 : r.b1;
-    uint32_t *di = from_b ? r.ia : r.ib;
+    const Rec *src = from_b ? r.b : r.a;
+    Rec *dst = from_b ? r.a : r.b;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, w = tid >> 5;
 
     for (;;) {
@@ -164,17 +182,15 @@ __global__ void __launch_bounds__(256) sort_pass_kernel(Records r, const uint32_
         if (tile >= ntiles) break;
         for (int i = tid; i < 8 * 256; i += 256) (&wcnt[0][0])[i] = 0u;
         __syncthreads();
-        uint64_t k0[8], k1[8];
-        uint32_t ix[8], dg[8], rk[8];
+        ulonglong4 rec[8];                 // {be0, be1, count, len | lidx << 32}
+        uint32_t dg[8], rk[8];
         const unsigned long long tbase = (unsigned long long)tile * kSortTile + w * 256u + lane;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const unsigned long long e = tbase + i * 32u;
             const bool valid = e < n;
-            k0[i] = valid ? s0[e] : 0ull;
-            k1[i] = valid ? s1[e] : 0ull;
-            ix[i] = valid ? si[e] : 0u;
-            dg[i] = valid ? digit_of(k0[i], k1[i], pass) : 0x100u;
+            rec[i] = valid ? *reinterpret_cast<const ulonglong4 *>(src + e) : make_ulonglong4(0ull, 0ull, 0ull, 0ull);
+            dg[i] = valid ? digit_of(rec[i].x, rec[i].y, pass) : 0x100u;
         }
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -210,7 +226,7 @@ __global__ void __launch_bounds__(256) sort_pass_kernel(Records r, const uint32_
         for (int i = 0; i < 8; ++i) {
             if (dg[i] < 256u) {
                 const uint32_t pos = tile_base[dg[i]] + wcnt[w][dg[i]] + rk[i];
-                d0[pos] = k0[i]; d1[pos] = k1[i]; di[pos] = ix[i];
+                *reinterpret_cast<ulonglong4 *>(dst + pos) = rec[i];
             }
         }
         __syncthreads();
@@ -219,13 +235,16 @@ __global__ void __launch_bounds__(256) sort_pass_kernel(Records r, const uint32_
 }
 
 // ---- keys longer than 16 bytes ---------------------------------------------------
-// order of two keys that agree on their first 16 bytes
-LC_D int cmp_tail(const LongTok &a, const LongTok &b) {
-    const uint64_t la = a.len, lb = b.len;
-    const uint64_t m = la < lb ? la : lb;
-    for (uint64_t i = 16; i < m; ++i) {
-        const uint32_t x = a.ptr[i], y = b.ptr[i];
-        if (x != y) return x < y ? -1 : 1;
+// order of two records that agree on their first 16 bytes
+LC_D int cmp_tail(const Records &r, const Rec &a, const Rec &b) {
+    const uint32_t la = a.len, lb = b.len;
+    const uint32_t m = la < lb ? la : lb;
+    if (m > 16u) {
+        const uint8_t *pa = r.longs[a.lidx].ptr, *pb = r.longs[b.lidx].ptr;
+        for (uint32_t i = 16; i < m; ++i) {
+            const uint32_t x = pa[i], y = pb[i];
+            if (x != y) return x < y ? -1 : 1;
+        }
     }
     return la < lb ? -1 : (la > lb ? 1 : 0);
 }
@@ -234,28 +253,25 @@ LC_D int cmp_tail(const LongTok &a, const LongTok &b) {
 // bytes is put in full-key order by the thread that owns the run's first record.
 __global__ void __launch_bounds__(256) tie_fix_kernel(Records r, const Counters *ctr) {
     const unsigned long long n = ctr->n_entries;
-    const bool in_b = ctr->sort_parity != 0u;
-    const uint64_t *s0 = in_b ? r.b0 : r.a0, *s1 = in_b ? r.b1 : r.a1;
-    uint32_t *si = in_b ? r.ib : r.ia;
+    Rec *s = ctr->sort_parity != 0u ? r.b : r.a;
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i + 1 < n;
          i += (unsigned long long)gridDim.x * blockDim.x) {
-        const uint64_t a = s0[i], b = s1[i];
+        const uint64_t a = s[i].be0, b = s[i].be1;
         if ((b & 0xFFull) == 0ull) continue;                          // key shorter than 16 bytes
-        if (i > 0 && s0[i - 1] == a && s1[i - 1] == b) continue;      // not the first of its run
-        if (s0[i + 1] != a || s1[i + 1] != b) continue;               // run of one
+        if (i > 0 && s[i - 1].be0 == a && s[i - 1].be1 == b) continue;      // not the first of its run
+        if (s[i + 1].be0 != a || s[i + 1].be1 != b) continue;               // run of one
         unsigned long long j = i + 2;
-        while (j < n && s0[j] == a && s1[j] == b) ++j;
-        // insertion sort of si[i..j) by full key
+        while (j < n && s[j].be0 == a && s[j].be1 == b) ++j;
+        // insertion sort of s[i..j) by full key
         for (unsigned long long x = i + 1; x < j; ++x) {
-            const uint32_t v = si[x];
-            const LongTok tv = r.ref[v];
+            const Rec v = s[x];
             unsigned long long y = x;
             while (y > i) {
-                const uint32_t u = si[y - 1];
-                if (cmp_tail(r.ref[u], tv) <= 0) break;
-                si[y] = u; --y;
+                const Rec u = s[y - 1];
+                if (cmp_tail(r, u, v) <= 0) break;
+                s[y] = u; --y;
             }
-            si[y] = v;
+            s[y] = v;
         }
     }
 }
@@ -270,7 +286,7 @@ static inline unsigned grid_for(uint64_t n, unsigned per_block, int num_sms, int
 }
 
 int launch_extract(const Slot *table, uint64_t slots, Records r, Counters *ctr, int num_sms, cudaStream_t st) {
-    extract_kernel<<<grid_for(slots, 256 * 4, num_sms, 8), 256, 0, st>>>(table, slots, r, ctr);
+    extract_kernel<<<grid_for(slots, 1024, num_sms, 8), 256, 0, st>>>(table, slots, r, ctr);
     return 1;
 }
 

@@ -48,20 +48,22 @@ __global__ void __launch_bounds__(256) scan_u64_kernel(const unsigned long long 
         unsigned long long woff = 0, agg = 0;
 #pragma unroll
         for (int k = 0; k < 8; ++k) { if ((uint32_t)k < w) woff += warp_sum[k]; agg += warp_sum[k]; }
-        if (tid == 0) {
+        if (w == 0) {                          // the first warp chains this tile to its predecessors
             uint64_t *st = lb_state + tile;
             unsigned long long prefix = 0;
             if (tile == 0) {
-                lb_store(st, lb_pack(epoch, kLbInclusive, agg));
+                if (lane == 0) lb_store(st, lb_pack(epoch, kLbInclusive, agg));
             } else {
-                lb_store(st, lb_pack(epoch, kLbAggregate, agg));
-                prefix = lb_lookback(lb_state, tile, 1u, 0u, epoch);
-                lb_store(st, lb_pack(epoch, kLbInclusive, prefix + agg));
+                if (lane == 0) lb_store(st, lb_pack(epoch, kLbAggregate, agg));
+                prefix = lb_lookback_warp(lb_state, tile, epoch, lane);
+                if (lane == 0) lb_store(st, lb_pack(epoch, kLbInclusive, prefix + agg));
             }
-            tile_prefix = prefix;
-            if (tile == ntiles - 1) {
-                if (total) *total = prefix + agg;
-                if (append_total) out[n] = prefix + agg;
+            if (lane == 0) {
+                tile_prefix = prefix;
+                if (tile == ntiles - 1) {
+                    if (total) *total = prefix + agg;
+                    if (append_total) out[n] = prefix + agg;
+                }
             }
         }
         __syncthreads();
@@ -88,33 +90,32 @@ int launch_exclusive_scan_u64(const unsigned long long *in, unsigned long long *
 }
 
 // ---- run heads -----------------------------------------------------------------------
-LC_D bool same_key(uint64_t a0, uint64_t a1, const LongTok &ra, uint64_t b0, uint64_t b1, const LongTok &rb) {
-    if (a0 != b0 || a1 != b1) return false;
-    if (ra.len != rb.len) return false;
-    if (ra.len <= 16) return true;
-    for (uint64_t i = 16; i < ra.len; ++i)
-        if (ra.ptr[i] != rb.ptr[i]) return false;
+LC_D bool same_key(const Records &r, const Rec &a, const Rec &b) {
+    if (a.be0 != b.be0 || a.be1 != b.be1 || a.len != b.len) return false;
+    if (a.len <= 16u) return true;
+    const uint8_t *pa = r.longs[a.lidx].ptr, *pb = r.longs[b.lidx].ptr;
+    for (uint32_t i = 16; i < a.len; ++i)
+        if (pa[i] != pb[i]) return false;
     return true;
 }
 
 __global__ void __launch_bounds__(256) head_kernel(Records r, ReduceBufs o, const Counters *ctr) {
     const unsigned long long n = ctr->n_entries;
-    const bool in_b = ctr->sort_parity != 0u;
-    const uint64_t *s0 = in_b ? r.b0 : r.a0, *s1 = in_b ? r.b1 : r.a1;
-    const uint32_t *si = in_b ? r.ib : r.ia;
+    const Rec *s = ctr->sort_parity != 0u ? r.b : r.a;
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
          i += (unsigned long long)gridDim.x * blockDim.x) {
+        const Rec cur = s[i];
         bool head = true;
         if (i > 0) {
-            const uint64_t a0 = s0[i - 1], a1 = s1[i - 1], b0 = s0[i], b1 = s1[i];
-            if (a0 == b0 && a1 == b1) {
-                if ((b1 & 0xFFull) == 0ull) head = false;              // shorter than 16 bytes: prefix is the key
-                else head = !same_key(a0, a1, r.ref[si[i - 1]], b0, b1, r.ref[si[i]]);
+            const Rec prev = s[i - 1];
+            if (prev.be0 == cur.be0 && prev.be1 == cur.be1) {
+                if ((cur.be1 & 0xFFull) == 0ull) head = false;          // shorter than 16 bytes: prefix is the key
+                else head = !same_key(r, prev, cur);
             }
         }
         o.head[i] = head ? 1 : 0;
         o.rank[i] = head ? 1ull : 0ull;
-        o.csum[i] = r.count[si[i]];                 // counts in sorted order, prefix-summed next
+        o.csum[i] = cur.count;                      // counts in sorted order, prefix-summed next
     }
 }
 
@@ -123,13 +124,12 @@ __global__ void __launch_bounds__(256) head_kernel(Records r, ReduceBufs o, cons
 // it is the difference of two entries of the prefix sum over the sorted counts.
 __global__ void __launch_bounds__(256) run_heads_kernel(Records r, ReduceBufs o, const Counters *ctr) {
     const unsigned long long n = ctr->n_entries;
-    const bool in_b = ctr->sort_parity != 0u;
-    const uint32_t *si = in_b ? r.ib : r.ia;
+    const Rec *s = ctr->sort_parity != 0u ? r.b : r.a;
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
          i += (unsigned long long)gridDim.x * blockDim.x) {
         if (!o.head[i]) continue;
         const unsigned long long out = o.rank[i];
-        o.key_offsets[out] = r.ref[si[i]].len;
+        o.key_offsets[out] = s[i].len;
         o.src_pos[out] = (uint32_t)i;
     }
 }
@@ -138,9 +138,7 @@ __global__ void __launch_bounds__(256) run_heads_kernel(Records r, ReduceBufs o,
 // by the records' counts), and the key bytes
 __global__ void __launch_bounds__(256) blob_kernel(Records r, ReduceBufs o, Counters *ctr) {
     const unsigned long long n_out = ctr->n_out, n = ctr->n_entries;
-    const bool in_b = ctr->sort_parity != 0u;
-    const uint64_t *s0 = in_b ? r.b0 : r.a0, *s1 = in_b ? r.b1 : r.a1;
-    const uint32_t *si = in_b ? r.ib : r.ia;
+    const Rec *s = ctr->sort_parity != 0u ? r.b : r.a;
     for (unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; k < n_out;
          k += (unsigned long long)gridDim.x * blockDim.x) {
         const uint32_t pos = o.src_pos[k];
@@ -151,12 +149,12 @@ __global__ void __launch_bounds__(256) blob_kernel(Records r, ReduceBufs o, Coun
         const uint64_t off = o.key_offsets[k], len = o.key_offsets[k + 1] - off;
         if (off + len > o.blob_cap) { atomicOr(&ctr->status, kStatusBlobFull); continue; }
         uint8_t *dst = o.key_blob + off;
+        const Rec rec = s[pos];
         if (len <= 16) {
-            const uint64_t b0 = s0[pos], b1 = s1[pos];
             for (uint32_t b = 0; b < (uint32_t)len; ++b)
-                dst[b] = (uint8_t)(b < 8 ? b0 >> (56 - 8 * b) : b1 >> (56 - 8 * (b - 8)));
+                dst[b] = (uint8_t)(b < 8 ? rec.be0 >> (56 - 8 * b) : rec.be1 >> (56 - 8 * (b - 8)));
         } else {
-            const uint8_t *src = r.ref[si[pos]].ptr;
+            const uint8_t *src = r.longs[rec.lidx].ptr;
             for (uint64_t b = 0; b < len; ++b) dst[b] = src[b];
         }
     }
