@@ -270,6 +270,7 @@ def main():
     ms, map_ms, shuf = timed(text, args.steps)
     m1 = sampler.mark()
     st = wc.stats()
+    stage_last = dict(zip(("map", "process", "reduce"), wc.stage_ms()))
     launches_per_step = st["kernel_launches"]
     uniq, tokens = st["unique_keys"], st["tokens"]
     value = total * args.steps / (ms * 1e-3) / GB
@@ -367,7 +368,7 @@ def main():
                            "l2": "input per step (%d MiB per GPU) is larger than the 126 MB L2" % (per_gpu >> 20)},
                 "roofline": roofline, "shuffle": shuffle, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
                 "gpu_launches": launches_per_step * args.steps, "gpu_launches_per_step": launches_per_step,
-                "stage_ms_last_step": dict(zip(("map", "process", "reduce"), wc.stage_ms()))}
+                "stage_ms_last_step": stage_last}
         print(json.dumps(line), flush=True)
     wc.close()
     if world > 1:
