@@ -391,7 +391,7 @@ int locust_create(const locust_config *cfg, locust_ctx **out) {
     *c->h_xflag = 0;
     CU(cudaMallocHost(reinterpret_cast<void **>(&c->h_ctr), sizeof(Counters)));
     memset(c->h_ctr, 0, sizeof(Counters));
-    CU(dalloc(&c->sort.hist, 16 * 256));
+    CU(dalloc(&c->sort.hist, 16 * 256 + 16));
     CU(dalloc(&c->sort.bases, 16 * 256));
     CU(dalloc(&c->sort.tickets, 64));
     CU(cudaMemsetAsync(c->sort.tickets, 0, 64 * sizeof(uint32_t), c->stream));

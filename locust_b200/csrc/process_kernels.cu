@@ -163,10 +163,8 @@ __global__ void __launch_bounds__(256) sort_prep_kernel(const uint32_t *hist, ui
 // (warp match + per-warp digit counters), its digit totals are chained to the
 // previous tiles' by decoupled look-back, and the records are scattered to their
 // final place for this digit.  Stable.
-__global__ void __launch_bounds__(256) sort_pass_kernel(Records r, const uint32_t *__restrict__ bases,
-                                                        const Counters *ctr, int pass, uint64_t *lb_state,
-                                                        uint32_t *ticket, uint32_t epoch) {
-    if (!ctr->pass_active[pass]) return;
+LC_D void sort_one_pass(const Records &r, const uint32_t *__restrict__ bases, const Counters *ctr, int pass,
+                        uint64_t *lb_state, uint32_t *ticket, uint32_t epoch) {
     __shared__ uint32_t wcnt[8][256];
     __shared__ uint32_t tile_base[256];
     __shared__ uint32_t tslot;
@@ -234,6 +232,42 @@ __global__ void __launch_bounds__(256) sort_pass_kernel(Records r, const uint32_
     return_ticket(ticket);
 }
 
+// One launch per pass (fallback when a cooperative launch is not possible).
+__global__ void __launch_bounds__(256) sort_pass_kernel(Records r, const uint32_t *__restrict__ bases,
+                                                        const Counters *ctr, int pass, uint64_t *lb_state,
+                                                        uint32_t *ticket, uint32_t epoch) {
+    if (!ctr->pass_active[pass]) return;
+    sort_one_pass(r, bases, ctr, pass, lb_state, ticket, epoch);
+}
+
+// All passes in one cooperative launch: between passes the whole grid meets at a barrier (every
+// record of pass p must be in place before pass p + 1 reads it).  Passes that would move nothing
+// cost nothing, and a pass no longer pays a kernel launch -- with 50 000 records that was most
+// of its time.  *bar counts arrivals; the host zeroes it before the launch.
+__global__ void __launch_bounds__(256) sort_all_kernel(Records r, const uint32_t *__restrict__ bases,
+                                                       const Counters *ctr, uint64_t *lb_state, uint32_t *tickets,
+                                                       uint32_t epoch, uint32_t *bar) {
+    uint32_t generation = 0;
+    for (int pass = 0; pass < 16; ++pass) {
+        if (!ctr->pass_active[pass]) continue;                      // the same decision in every block
+        sort_one_pass(r, bases, ctr, pass, lb_state, tickets + 2 * pass, epoch + (uint32_t)pass);
+        ++generation;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            atomicAdd(bar, 1u);
+            const uint32_t want = generation * gridDim.x;
+            uint32_t seen;
+            do {
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(bar) : "memory");
+                if (seen < want) __nanosleep(100);
+            } while (seen < want);
+            __threadfence();
+        }
+        __syncthreads();
+    }
+}
+
 // ---- keys longer than 16 bytes ---------------------------------------------------
 // order of two records that agree on their first 16 bytes
 LC_D int cmp_tail(const Records &r, const Rec &a, const Rec &b) {
@@ -298,9 +332,29 @@ int launch_append_long(const LongOcc *list, uint64_t long_cap, Records r, Counte
 }
 
 int launch_sort_records(Records r, SortScratch s, Counters *ctr, uint32_t epoch, int num_sms, cudaStream_t st) {
-    cudaMemsetAsync(s.hist, 0, 16 * 256 * sizeof(uint32_t), st);
+    // hist holds the 16 x 256 digit counters and, behind them, the grid barrier's arrival counter
+    cudaMemsetAsync(s.hist, 0, (16 * 256 + 16) * sizeof(uint32_t), st);
     sort_hist_kernel<<<grid_for(r.cap, 256 * 8, num_sms, 4), 256, 0, st>>>(r, ctr, s.hist);
     sort_prep_kernel<<<1, 256, 0, st>>>(s.hist, s.bases, ctr);
+    static int resident_per_sm = -1;        // blocks of sort_all_kernel that fit one SM (same for every device here)
+    if (resident_per_sm < 0) {
+        int nb = 0, coop = 0, dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, sort_all_kernel, 256, 0) != cudaSuccess) nb = 0;
+        resident_per_sm = coop ? nb : 0;
+    }
+    if (resident_per_sm > 0) {
+        unsigned g = grid_for(r.cap, kSortTile, num_sms, resident_per_sm);
+        uint32_t *bar = s.hist + 16 * 256;
+        const uint32_t *bases = s.bases;
+        const Counters *cctr = ctr;
+        void *args[] = {&r, &bases, &cctr, &s.lb_state, &s.tickets, &epoch, &bar};
+        if (cudaLaunchCooperativeKernel(reinterpret_cast<void *>(sort_all_kernel), dim3(g), dim3(256), args, 0, st) ==
+            cudaSuccess)
+            return 3;
+        cudaGetLastError();                 // fall through to one launch per pass
+    }
     const unsigned g = grid_for(r.cap, kSortTile, num_sms, 4);
     for (int p = 0; p < 16; ++p)
         sort_pass_kernel<<<g, 256, 0, st>>>(r, s.bases, ctr, p, s.lb_state, s.tickets + 2 * p, epoch + (uint32_t)p);
