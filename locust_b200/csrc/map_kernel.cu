@@ -59,9 +59,11 @@ LC_D void cas128(Slot *s, uint64_t n0, uint64_t n1, uint64_t &o0, uint64_t &o1) 
 }
 
 // Adds `inc` occurrences of key (k0, k1) to the global table.
+// kPlain: the job runs with flags == 0, so no test switch has to be looked at.
+template <bool kPlain>
 __device__ __noinline__ void global_insert(const MapParams &p, uint64_t k0, uint64_t k1, unsigned long long inc) {
     uint64_t h = hash_key128(k0, k1);
-    if (p.flags & LOCUST_F_WEAK_HASH) h &= 0xFFull;
+    if (!kPlain && (p.flags & LOCUST_F_WEAK_HASH)) h &= 0xFFull;
     uint64_t slot = h & p.table_mask;
     for (uint32_t probe = 0; probe < kMaxProbe; ++probe) {
         Slot *s = p.table + slot;
@@ -92,27 +94,42 @@ struct WarpCtx {
 #define WC_DESC(wc) reinterpret_cast<uint16_t *>(smem_raw + (wc).area + kDescOff)
 #define WC_QUEUE(wc) reinterpret_cast<ulonglong2 *>(smem_raw + (wc).area + kQueueOff)
 
-// Counts a token of <= 8 bytes (key = lo | hi << 32, never 0) in the CTA's table.
-// One 128-bit load reads both ways of the bucket.  False if the bucket is taken by
-// two other keys (or a claim was lost): the caller sends the key to the global table.
-LC_D bool smem_insert(const WarpCtx &wc, uint32_t lo, uint32_t hi) {
-    const uint32_t h = lo * 0x9E3779B1u + hi * 0x85EBCA77u;
-    const uint32_t b = __umulhi(h, kBuckets);
+// The CTA's table counts tokens of <= 8 bytes (key = lo | hi << 32, never 0); a bucket is two
+// keys side by side, so one 128-bit load reads both ways.
+LC_D uint32_t smem_bucket(uint32_t lo, uint32_t hi) {
+    return __umulhi(lo * 0x9E3779B1u + hi * 0x85EBCA77u, kBuckets);
+}
+// Fast probe used per token: counts the token if its key already sits in the bucket, without
+// a divergent branch.  A miss is queued by the caller; the queue's drain claims free ways.
+LC_D bool smem_hit(const WarpCtx &wc, uint32_t lo, uint32_t hi) {
+    const uint32_t b = smem_bucket(lo, hi);
     const unsigned long long k = (unsigned long long)lo | ((unsigned long long)hi << 32);
     const ulonglong2 kb = WC_SKEYS[b];
-    if (kb.x == k) { atomicAdd(&WC_SCNT[2 * b], 1u); return true; }
-    if (kb.y == k) { atomicAdd(&WC_SCNT[2 * b + 1], 1u); return true; }
+    const bool h1 = kb.y == k;
+    const bool hit = h1 || kb.x == k;
+    if (hit) atomicAdd(&WC_SCNT[2 * b + (h1 ? 1u : 0u)], 1u);
+    return hit;
+}
+// Full insert: counts `inc` occurrences, claiming a free way if the key is not there yet.  False
+// if the bucket is taken by two other keys (or a claim was lost): the key goes to the global table.
+LC_D bool smem_insert(const WarpCtx &wc, uint32_t lo, uint32_t hi, uint32_t inc) {
+    const uint32_t b = smem_bucket(lo, hi);
+    const unsigned long long k = (unsigned long long)lo | ((unsigned long long)hi << 32);
+    const ulonglong2 kb = WC_SKEYS[b];
+    if (kb.x == k) { atomicAdd(&WC_SCNT[2 * b], inc); return true; }
+    if (kb.y == k) { atomicAdd(&WC_SCNT[2 * b + 1], inc); return true; }
     if (kb.x == 0ull || kb.y == 0ull) {
         const uint32_t way = kb.x == 0ull ? 0u : 1u;
         unsigned long long *slot = reinterpret_cast<unsigned long long *>(WC_SKEYS) + 2 * b + way;
         const unsigned long long old = atomicCAS(slot, 0ull, k);
-        if (old == 0ull || old == k) { atomicAdd(&WC_SCNT[2 * b + way], 1u); return true; }
+        if (old == 0ull || old == k) { atomicAdd(&WC_SCNT[2 * b + way], inc); return true; }
     }
     return false;
 }
 
 // Byte-serial path for one token starting at base[pos]: tokens longer than 16 bytes
 // and the LOCUST_F_GENERIC_TOKENISER test switch.
+template <bool kPlain>
 __device__ __noinline__ void token_generic(const MapParams &p, const WarpCtx &wc, uint64_t pos) {
     const uint8_t *s = p.base + pos;
     const uint64_t maxlen = p.hi - pos;
@@ -131,10 +148,10 @@ __device__ __noinline__ void token_generic(const MapParams &p, const WarpCtx &wc
         else atomicOr(&p.ctr->status, kStatusLongFull);
         return;
     }
-    if (L <= 8 && wc.use_smem) {
-        if (smem_insert(wc, (uint32_t)k0, (uint32_t)(k0 >> 32))) return;
+    if (L <= 8 && (kPlain || wc.use_smem)) {
+        if (smem_insert(wc, (uint32_t)k0, (uint32_t)(k0 >> 32), 1u)) return;
     }
-    global_insert(p, k0, k1, 1ull);
+    global_insert<kPlain>(p, k0, k1, 1ull);
 }
 
 // Chunk at byte offset `off` that straddles lo or hi: bytes outside [lo, hi) read as '\n'.
@@ -160,6 +177,7 @@ LC_D uint4 load_chunk(const MapParams &p, uint64_t row, uint32_t lane) {
     return v;
 }
 
+template <bool kPlain>
 LC_D void drain_queue(const MapParams &p, WarpCtx &wc, uint32_t keep_below) {
     // Pops batches of up to 32 keys until fewer than keep_below remain.  Equal keys of a
     // batch are added up first and inserted once: a heavy-hitter word of 9..16 bytes would
@@ -178,9 +196,13 @@ LC_D void drain_queue(const MapParams &p, WarpCtx &wc, uint32_t keep_below) {
         const unsigned long long lx = __shfl_sync(kFull, k.x, leader), ly = __shfl_sync(kFull, k.y, leader);
         const bool same = k.x == lx && k.y == ly;                  // equal hash, equal key (else: insert alone)
         const uint32_t agg = __ballot_sync(kFull, same) & peers;
-        if (valid) {
-            if (!same) global_insert(p, k.x, k.y, 1ull);
-            else if (wc.lane == leader) global_insert(p, k.x, k.y, (unsigned long long)__popc(agg));
+        // one lane per distinct key carries the sum; short keys get a chance to claim a free way
+        // of the CTA's table first (the only place ways are claimed on the fast path)
+        const uint32_t inc = !same ? 1u : (wc.lane == leader ? (uint32_t)__popc(agg) : 0u);
+        if (valid && inc) {
+            const bool to_smem = k.y == 0ull && (kPlain || wc.use_smem) &&
+                                 smem_insert(wc, (uint32_t)k.x, (uint32_t)(k.x >> 32), inc);
+            if (!to_smem) global_insert<kPlain>(p, k.x, k.y, (unsigned long long)inc);
         }
         wc.qn -= take;
         __syncwarp();
@@ -189,7 +211,10 @@ LC_D void drain_queue(const MapParams &p, WarpCtx &wc, uint32_t keep_below) {
 
 // Phase B for one batch: lane `wc.lane` takes token number t of the row (if active).
 // All lanes call this together.
-LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active, uint32_t t, uint64_t row_pos) {
+template <bool kPlain>
+LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active, uint32_t t, const uint8_t *rowp) {
+    // rowp = this lane's 16 bytes of the row; the row's byte offset is only needed for tokens longer than 16 bytes
+#define ROW_POS() ((uint64_t)(rowp - p.base) - wc.lane * 16u)
     const uint32_t *row32 = reinterpret_cast<const uint32_t *>(WC_ROW(wc));
     const uint32_t pos = active ? WC_DESC(wc)[t] : 0u;
     // token length: first delimiter at or after pos, within 17 bits
@@ -204,7 +229,7 @@ LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active
     uint32_t a, b, c, d;
     if (ascii) extract_key16_ascii(w0, w1, w2, w3, w4, o, L, a, b, c, d);      // warp-uniform branch
     else extract_key16_any(w0, w1, w2, w3, w4, o, L, a, b, c, d);
-    if (p.flags & LOCUST_F_SORT_PATH) {          // alternative path: one record per token, no combiner
+    if (!kPlain && (p.flags & LOCUST_F_SORT_PATH)) {          // alternative path: one record per token, no combiner
         const uint32_t m = __ballot_sync(kFull, has);
         unsigned long long base = 0;
         if (wc.lane == 0 && m) base = atomicAdd(&p.ctr->n_entries, (unsigned long long)__popc(m));
@@ -222,27 +247,29 @@ LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active
             }
         }
         if (__any_sync(kFull, far)) {
-            if (far) token_generic(p, wc, row_pos + pos);
+            if (far) token_generic<kPlain>(p, wc, ROW_POS() + pos);
             __syncwarp();
         }
         return;
     }
     bool defer = has;
-    if (has && L <= 8u && wc.use_smem) defer = !smem_insert(wc, a, b);
+    if (has && L <= 8u && (kPlain || wc.use_smem)) defer = !smem_hit(wc, a, b);
     const uint32_t m = __ballot_sync(kFull, defer);
     if (m) {
         if (defer)
             WC_QUEUE(wc)[wc.qn + __popc(m & ((1u << wc.lane) - 1u))] =
                 make_ulonglong2((uint64_t)a | ((uint64_t)b << 32), (uint64_t)c | ((uint64_t)d << 32));
         wc.qn += __popc(m);
-        if (wc.qn >= 32u) drain_queue(p, wc, 32u);
+        if (wc.qn >= 32u) drain_queue<kPlain>(p, wc, 32u);
     }
     if (__any_sync(kFull, far)) {
-        if (far) token_generic(p, wc, row_pos + pos);
+        if (far) token_generic<kPlain>(p, wc, ROW_POS() + pos);
         __syncwarp();
     }
+#undef ROW_POS
 }
 
+template <bool kPlain>
 __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const __grid_constant__ MapParams p) {
     {
         uint4 *z = reinterpret_cast<uint4 *>(smem_raw);
@@ -259,12 +286,12 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
     // where token density varies along the file (BASELINE config 5) each warp still sees an
     // average mix, and pieces stay long enough that their start-up cost does not matter.
     const uint64_t seg_len = (nrows + nwarps * kSegments - 1) / (nwarps * kSegments);
-    const bool use_fast = !(p.flags & LOCUST_F_GENERIC_TOKENISER);
+    const bool use_fast = kPlain || !(p.flags & LOCUST_F_GENERIC_TOKENISER);
     WarpCtx wc;
     wc.area = kKeysBytes + kCntBytes + warp * kWarpArea;
     wc.qn = 0u;
     wc.lane = lane;
-    wc.use_smem = !(p.flags & LOCUST_F_NO_SMEM_COMBINER);
+    wc.use_smem = kPlain || !(p.flags & LOCUST_F_NO_SMEM_COMBINER);
     uint16_t *bits16 = reinterpret_cast<uint16_t *>(WC_BITS(wc));
 
     for (uint32_t seg = 0; seg < kSegments; ++seg) {
@@ -272,8 +299,25 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
         uint64_t r1 = r0 + seg_len;
         if (r1 > row_lo + nrows) r1 = row_lo + nrows;
         if (r0 >= r1) break;
-        uint4 c = load_chunk(p, r0, lane);
-        uint4 n = load_chunk(p, r0 + 1, lane);
+        const uint32_t n_rows = (uint32_t)(r1 - r0);
+        // Rows counted from r0 from here on.  Rows [f0, f0 + flen) lie entirely inside [lo, hi) and
+        // are loaded without any bounds arithmetic; the few others (the first row of an unaligned
+        // range, the rows around hi) go through load_chunk.
+        uint32_t f0, flen;
+        {
+            const uint64_t full_lo = (p.lo + 511ull) >> 9, full_hi = p.hi >> 9, lim = (uint64_t)n_rows + 2ull;
+            const uint64_t a = full_lo > r0 ? (full_lo - r0 < lim ? full_lo - r0 : lim) : 0ull;
+            const uint64_t b = full_hi > r0 ? (full_hi - r0 < lim ? full_hi - r0 : lim) : 0ull;
+            f0 = (uint32_t)a;
+            flen = b > a ? (uint32_t)(b - a) : 0u;
+        }
+        const uint8_t *q = p.base + r0 * 512ull + lane * 16u;              // this lane's bytes of row r0
+        auto load_row = [&](uint32_t i) -> uint4 {
+            if (i - f0 < flen) return ldg_stream(q + (uint64_t)i * 512ull);
+            return load_chunk(p, r0 + i, lane);
+        };
+        uint4 c = load_row(0u);
+        uint4 n = load_row(1u);
         uint32_t dc = classify16(c.x, c.y, c.z, c.w);
         uint32_t dn = classify16(n.x, n.y, n.z, n.w);
         bool asc_c = !__any_sync(kFull, (c.x | c.y | c.z | c.w) & 0x80808080u);
@@ -284,11 +328,11 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
             const uint64_t b = r0 * 512ull;
             pd = (b <= p.lo || is_delim(p.base[b - 1])) ? 0x8000u : 0u;
         }
-        for (uint64_t row = r0; row < r1; ++row) {
-            const uint4 nn = load_chunk(p, row + 2, lane);                 // in flight while this row is tokenised
+        for (uint32_t i = 0; i < n_rows; ++i) {
+            const uint4 nn = load_row(i + 2u);                             // in flight while this row is tokenised
             const uint32_t d_dn = __shfl_sync(kFull, lane == 31 ? pd : dc, (lane + 31) & 31);
             uint32_t starts = ~dc & ((dc << 1) | (d_dn >> 15)) & 0xFFFFu;
-            const uint64_t row_pos = row * 512ull;
+            const uint8_t *rowp = q + (uint64_t)i * 512ull;
             if (use_fast) {
                 // A: stage bytes and delimiter bits (with the next row's first chunks as look-ahead)
                 reinterpret_cast<uint4 *>(WC_ROW(wc))[lane] = c;
@@ -313,13 +357,13 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
                 // B: one token per lane, 32 at a time
                 const bool ascii = asc_c && asc_n;
 #pragma unroll 1
-                for (uint32_t t0 = 0; t0 < total; t0 += 32) process_batch(p, wc, ascii, t0 + lane < total, t0 + lane, row_pos);
+                for (uint32_t t0 = 0; t0 < total; t0 += 32) process_batch<kPlain>(p, wc, ascii, t0 + lane < total, t0 + lane, rowp);
                 __syncwarp();
             } else {
                 while (starts) {
                     const uint32_t pp = (uint32_t)__ffs((int)starts) - 1u;
                     starts &= starts - 1u;
-                    token_generic(p, wc, row_pos + lane * 16u + pp);
+                    token_generic<kPlain>(p, wc, (uint64_t)(rowp - p.base) + pp);
                 }
                 __syncwarp();
             }
@@ -329,13 +373,13 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
             asc_n = !__any_sync(kFull, (n.x | n.y | n.z | n.w) & 0x80808080u);
         }
     }
-    drain_queue(p, wc, 1u);
+    drain_queue<kPlain>(p, wc, 1u);
     __syncthreads();
     // flush the CTA's combiner into the global table
     const unsigned long long *keys = reinterpret_cast<const unsigned long long *>(WC_SKEYS);
     for (uint32_t i = threadIdx.x; i < kSmemSlots; i += kMapThreads) {
         const unsigned long long k = keys[i];
-        if (k) global_insert(p, k, 0ull, (unsigned long long)WC_SCNT[i]);
+        if (k) global_insert<kPlain>(p, k, 0ull, (unsigned long long)WC_SCNT[i]);
     }
 }
 
@@ -356,7 +400,7 @@ __global__ void __launch_bounds__(256) shuffle_merge_kernel(const uint8_t *__res
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_short;
          i += (unsigned long long)gridDim.x * blockDim.x) {
         const ulonglong4 v = rec[i];
-        global_insert(p, v.x, v.y, v.z);
+        global_insert<false>(p, v.x, v.y, v.z);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {                      // long records are rare: one thread walks them
         const uint8_t *q = part + long_off;
@@ -388,7 +432,9 @@ int launch_shuffle_merge(const uint8_t *part, uint64_t nbytes, MapParams p, int 
 }
 
 cudaError_t map_kernel_setup() {
-    return cudaFuncSetAttribute(tokenize_combine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(tokenize_combine_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(tokenize_combine_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
 }
 
 int launch_tokenize_combine(const MapParams &p, int num_sms, cudaStream_t st) {
@@ -396,7 +442,8 @@ int launch_tokenize_combine(const MapParams &p, int num_sms, cudaStream_t st) {
     const uint64_t nrows = ((p.hi + 511ull) >> 9) - (p.lo >> 9);
     uint64_t ctas = (nrows + kMapWarps - 1) / kMapWarps;
     if (ctas > (uint64_t)num_sms) ctas = (uint64_t)num_sms;
-    tokenize_combine_kernel<<<(unsigned)ctas, kMapThreads, kSmemBytes, st>>>(p);
+    if (p.flags == 0u) tokenize_combine_kernel<true><<<(unsigned)ctas, kMapThreads, kSmemBytes, st>>>(p);
+    else tokenize_combine_kernel<false><<<(unsigned)ctas, kMapThreads, kSmemBytes, st>>>(p);
     return 1;
 }
 }  // namespace locust
