@@ -84,10 +84,22 @@ LC_HD uint32_t byte_perm(uint32_t a, uint32_t b, uint32_t s) {
 // ASCII variant (every byte of the window < 0x80): bytes past L are zeroed inside
 // the PRMT -- bit 3 of a selector nibble replicates the selected byte's sign bit,
 // which is 0x00 for any byte below 0x80.
+LC_HD uint32_t shl_clamp(uint32_t v, uint32_t n) {      // v << n, 0 for n >= 32
+#if defined(__CUDA_ARCH__)
+    uint32_t r;
+    asm("shl.b32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(n));   // PTX shl clamps the shift amount at 32
+    return r;
+#else
+    return n >= 32u ? 0u : v << n;
+#endif
+}
+// The 64-bit value 0x8888888888888888 << 4L (zlo = low word, zhi = high word) has nibble 8
+// exactly at the key bytes at or past L.  L >= 16 (and the "no delimiter" value 0xFFFFFFFF)
+// gives 0: nothing is zeroed.
 LC_HD void key_selectors(uint32_t o, uint32_t L, uint32_t &sel, uint32_t &zlo, uint32_t &zhi) {
     sel = 0x3210u + 0x1111u * o;
-    zlo = (L >= 8u) ? 0u : (0x88888888u << (4u * L));
-    zhi = (L >= 16u) ? 0u : ((L >= 8u) ? (0x88888888u << (4u * (L - 8u))) : 0x88888888u);
+    zlo = shl_clamp(0x88888888u, 4u * L);
+    zhi = shl_clamp(0x88888888u, 4u * (L > 8u ? L : 8u) - 32u);
 }
 LC_HD void extract_key16_ascii(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32_t w4, uint32_t o,
                                uint32_t L, uint32_t &a, uint32_t &b, uint32_t &c, uint32_t &d) {

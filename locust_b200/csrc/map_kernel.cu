@@ -103,11 +103,10 @@ LC_D uint32_t smem_bucket(uint32_t lo, uint32_t hi) {
 // a divergent branch.  A miss is queued by the caller; the queue's drain claims free ways.
 LC_D bool smem_hit(const WarpCtx &wc, uint32_t lo, uint32_t hi) {
     const uint32_t b = smem_bucket(lo, hi);
-    const unsigned long long k = (unsigned long long)lo | ((unsigned long long)hi << 32);
-    const ulonglong2 kb = WC_SKEYS[b];
-    const bool h1 = kb.y == k;
-    const bool hit = h1 || kb.x == k;
-    if (hit) atomicAdd(&WC_SCNT[2 * b + (h1 ? 1u : 0u)], 1u);
+    const uint4 kb = reinterpret_cast<const uint4 *>(WC_SKEYS)[b];
+    const uint32_t d0 = (kb.x ^ lo) | (kb.y ^ hi), d1 = (kb.z ^ lo) | (kb.w ^ hi);
+    const bool hit = d0 == 0u || d1 == 0u;
+    if (hit) atomicAdd(&WC_SCNT[2 * b + (d1 == 0u ? 1u : 0u)], 1u);
     return hit;
 }
 // Full insert: counts `inc` occurrences, claiming a free way if the key is not there yet.  False
@@ -348,10 +347,11 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
                     if (lane >= (uint32_t)o) incl += y;
                 }
                 const uint32_t total = __shfl_sync(kFull, incl, 31);
-                uint32_t at = incl - cnt;
+                uint32_t at = incl;                                         // filled from the back: order within a row is free
                 while (starts) {
-                    WC_DESC(wc)[at++] = (uint16_t)(lane * 16u + (uint32_t)__ffs((int)starts) - 1u);
-                    starts &= starts - 1u;
+                    const uint32_t top = 31u - (uint32_t)__clz((int)starts);
+                    WC_DESC(wc)[--at] = (uint16_t)(lane * 16u + top);
+                    starts ^= 1u << top;
                 }
                 __syncwarp();
                 // B: one token per lane, 32 at a time
