@@ -208,7 +208,7 @@ def main():
     torch.cuda.synchronize()
 
     stream = torch.cuda.Stream(device=dev)
-    table_log2 = args.table_log2 or (17 if name == "C2" else 22)
+    table_log2 = args.table_log2 or (20 if name == "C2" else 22)      # 20 is the library default
     wc = locust_b200.WordCount(device=local_rank, table_log2=table_log2, stream=stream.cuda_stream)
     if world > 1:
         from locust_b200.shuffle import DistributedWordCount, GpuBackend, PeerExchange
