@@ -163,20 +163,21 @@ __global__ void __launch_bounds__(256) sort_prep_kernel(const uint32_t *hist, ui
 // (warp match + per-warp digit counters), its digit totals are chained to the
 // previous tiles' by decoupled look-back, and the records are scattered to their
 // final place for this digit.  Stable.
-LC_D void sort_one_pass(const Records &r, const uint32_t *__restrict__ bases, const Counters *ctr, int pass,
-                        uint64_t *lb_state, uint32_t *ticket, uint32_t epoch) {
+// kStatic: tiles are dealt out by block index (tile = block, block + grid, ...) instead of by
+// ticket.  Only safe when every block of the grid is resident (cooperative launch): a tile waits
+// for lower-numbered tiles only, and those then belong to blocks that are running or done.
+LC_D void sort_one_pass(const bool kStatic, const Records &r, const uint32_t *__restrict__ bases, unsigned long long n,
+                        bool from_b, int pass, uint64_t *lb_state, uint32_t *ticket, uint32_t epoch) {
     __shared__ uint32_t wcnt[8][256];
     __shared__ uint32_t tile_base[256];
     __shared__ uint32_t tslot;
-    const unsigned long long n = ctr->n_entries;
     const uint32_t ntiles = (uint32_t)((n + kSortTile - 1) / kSortTile);
-    const bool from_b = ctr->pass_src[pass] != 0u;
     const Rec *src = from_b ? r.b : r.a;
     Rec *dst = from_b ? r.a : r.b;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, w = tid >> 5;
 
-    for (;;) {
-        const uint32_t tile = take_ticket(ticket, &tslot);
+    for (uint32_t round = 0;; ++round) {
+        const uint32_t tile = kStatic ? blockIdx.x + round * gridDim.x : take_ticket(ticket, &tslot);
         if (tile >= ntiles) break;
         for (int i = tid; i < 8 * 256; i += 256) (&wcnt[0][0])[i] = 0u;
         __syncthreads();
@@ -229,7 +230,7 @@ LC_D void sort_one_pass(const Records &r, const uint32_t *__restrict__ bases, co
         }
         __syncthreads();
     }
-    return_ticket(ticket);
+    if (!kStatic) return_ticket(ticket);
 }
 
 // One launch per pass (fallback when a cooperative launch is not possible).
@@ -237,7 +238,7 @@ __global__ void __launch_bounds__(256) sort_pass_kernel(Records r, const uint32_
                                                         const Counters *ctr, int pass, uint64_t *lb_state,
                                                         uint32_t *ticket, uint32_t epoch) {
     if (!ctr->pass_active[pass]) return;
-    sort_one_pass(r, bases, ctr, pass, lb_state, ticket, epoch);
+    sort_one_pass(false, r, bases, ctr->n_entries, ctr->pass_src[pass] != 0u, pass, lb_state, ticket, epoch);
 }
 
 // All passes in one cooperative launch: between passes the whole grid meets at a barrier (every
@@ -248,9 +249,17 @@ __global__ void __launch_bounds__(256) sort_all_kernel(Records r, const uint32_t
                                                        const Counters *ctr, uint64_t *lb_state, uint32_t *tickets,
                                                        uint32_t epoch, uint32_t *bar) {
     uint32_t generation = 0;
+    const unsigned long long n = ctr->n_entries;
+    uint32_t active = 0, from_b = 0;                                // the plan of sort_prep_kernel, read once
     for (int pass = 0; pass < 16; ++pass) {
-        if (!ctr->pass_active[pass]) continue;                      // the same decision in every block
-        sort_one_pass(r, bases, ctr, pass, lb_state, tickets + 2 * pass, epoch + (uint32_t)pass);
+        active |= (ctr->pass_active[pass] ? 1u : 0u) << pass;
+        from_b |= (ctr->pass_src[pass] ? 1u : 0u) << pass;
+    }
+    for (int pass = 0; pass < 16; ++pass) {
+        if (!((active >> pass) & 1u)) continue;                     // the same decision in every block
+        // few tiles (one round): dealt by block index, no ticket traffic; many tiles: tickets balance the load
+        sort_one_pass(n <= (unsigned long long)gridDim.x * kSortTile, r, bases, n, ((from_b >> pass) & 1u) != 0u, pass,
+                      lb_state, tickets + 2 * pass, epoch + (uint32_t)pass);
         ++generation;
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -260,7 +269,7 @@ __global__ void __launch_bounds__(256) sort_all_kernel(Records r, const uint32_t
             uint32_t seen;
             do {
                 asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(bar) : "memory");
-                if (seen < want) __nanosleep(100);
+                if (seen < want) __nanosleep(32);
             } while (seen < want);
             __threadfence();
         }
