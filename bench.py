@@ -168,6 +168,9 @@ def main():
     ap.add_argument("--cpu-sample-mib", type=int, default=32)
     ap.add_argument("--table-log2", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--final", default="ordered", choices=["ordered", "gather"],
+                    help="N>1: 'ordered' = parts are key ranges, every rank sorts its range, rank 0 concatenates the "
+                         "slices; 'gather' = hash parts, then everything is sent to rank 0 and sorted there")
     ap.add_argument("--shuffle", default="peers", choices=["peers", "nccl"],
                     help="N>1: 'peers' = packing kernel writes into the destination GPU's memory over NVLink "
                          "(fused pack+send), 'nccl' = pack locally, all_to_all_single")
@@ -227,7 +230,7 @@ def main():
             torch.cuda.synchronize()
             if int(ok.item()) == 0:
                 peers, args.shuffle = None, "nccl"
-        job = DistributedWordCount(GpuBackend(wc, dev), dist, peers=peers)
+        job = DistributedWordCount(GpuBackend(wc, dev), dist, peers=peers, ordered=args.final == "ordered")
         step = lambda buf: job.run(buf)
     else:
         step = lambda buf: wc.run(buf)
@@ -365,6 +368,7 @@ def main():
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic",
                 "config": {"workload": desc, "bytes_per_gpu": per_gpu, "tokens_per_gpu": tokens if world == 1 else None,
                            "unique_keys": uniq, "table_log2": table_log2, "input_sha256": input_id,
+                           "final_stage": (args.final if world > 1 else None),
                            "l2": "input per step (%d MiB per GPU) is larger than the 126 MB L2" % (per_gpu >> 20)},
                 "roofline": roofline, "shuffle": shuffle, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
                 "gpu_launches": launches_per_step * args.steps, "gpu_launches_per_step": launches_per_step,

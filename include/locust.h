@@ -191,6 +191,34 @@ int locust_shuffle_begin_merge(locust_ctx *ctx);
  * locust_reduce has returned). */
 int locust_shuffle_merge(locust_ctx *ctx, const void *dev_records, uint64_t nbytes);
 
+/* ---- ordered shuffle: ranks end up with consecutive key ranges --------------------------
+ * The reference's master node sorts everything again after reading its nodes' partial
+ * outputs (loadIntermediateFile + thrust::sort, main.cu:441, :415).  With parts that are key
+ * ranges instead of hash classes that last sort is not needed: rank r sorts and reduces range
+ * r alone, and the whole result is the ranks' results one after the other.
+ *
+ * After locust_map on every rank:
+ *   locust_partition_histogram adds, into dev_hist (device memory, uint64[LOCUST_PARTITION_BINS],
+ *     zeroed by the caller), how many of this rank's keys start with each two-byte prefix;
+ *   the caller sums dev_hist over all ranks (all-reduce);
+ *   locust_partition_by_range builds the prefix -> part map from the summed histogram (the same
+ *     on every rank): ranges follow key order and hold about the same number of keys, as far as
+ *     whole prefixes allow.  From then on locust_shuffle_sizes / _pack / _pack_peers with the
+ *     same nparts split by range instead of by hash, until locust_reset (or nparts = 0 here).
+ * After the exchange, locust_process and locust_reduce on every rank:
+ *   locust_result_part_bytes / locust_result_part_pack move a rank's result into one buffer
+ *     {n, key_bytes, total, part_bytes | key_offsets[n+1] | counts[n] | vals[n] | key bytes};
+ *   locust_result_concat, on the rank that wants the whole result, replaces its own result by
+ *     the given parts in order (its own part included), rebasing offsets and vals.  n_keys,
+ *     blob_bytes, totals: the first three header words of each part, host arrays. */
+#define LOCUST_PARTITION_BINS 65536u
+int locust_partition_histogram(locust_ctx *ctx, void *dev_hist);
+int locust_partition_by_range(locust_ctx *ctx, const void *dev_hist, uint32_t nparts);
+int locust_result_part_bytes(locust_ctx *ctx, uint64_t *bytes);
+int locust_result_part_pack(locust_ctx *ctx, void *dev_out);
+int locust_result_concat(locust_ctx *ctx, uint32_t nparts, const void *const *dev_parts, const uint64_t *n_keys,
+                         const uint64_t *blob_bytes, const uint64_t *totals);
+
 /* ---- for callers that cannot allocate ------------------------------------------
  * No counterpart in the reference (its main() allocates freely, main.cu:393,:402,:451).
  *

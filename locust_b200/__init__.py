@@ -26,8 +26,10 @@ EXPORTS = [
     "locust_last_error", "locust_shuffle_sizes", "locust_shuffle_pack",
     "locust_shuffle_begin_merge", "locust_shuffle_merge", "locust_count_static",
     "locust_map_intermediate", "locust_exchange_alloc", "locust_ipc_export", "locust_ipc_open", "locust_ipc_close",
-    "locust_shuffle_pack_peers",
+    "locust_shuffle_pack_peers", "locust_partition_histogram", "locust_partition_by_range",
+    "locust_result_part_bytes", "locust_result_part_pack", "locust_result_concat",
 ]
+PARTITION_BINS = 65536
 STATIC_MAX_KEYS = 16384
 STATIC_MAX_BYTES = 1 << 32
 
@@ -86,6 +88,11 @@ def load():
     L.locust_ipc_close.argtypes = [vp, vp]
     L.locust_shuffle_pack_peers.argtypes = [vp, u32, pp(vp), u64, u64]
     L.locust_count_static.argtypes = [vp, u64, vp, u64, pp(u64), vp, ctypes.c_char_p, ctypes.c_size_t]
+    L.locust_partition_histogram.argtypes = [vp, vp]
+    L.locust_partition_by_range.argtypes = [vp, vp, u32]
+    L.locust_result_part_bytes.argtypes = [vp, pp(u64)]
+    L.locust_result_part_pack.argtypes = [vp, vp]
+    L.locust_result_concat.argtypes = [vp, u32, pp(vp), pp(u64), pp(u64), pp(u64)]
     _lib = L
     return L
 
@@ -282,6 +289,30 @@ class WordCount:
         arr = (ctypes.c_void_p * len(dst_slots))(*dst_slots)
         self._check(self._L.locust_shuffle_pack_peers(self._h, len(dst_slots), arr, slot_bytes, short_cap),
                     "locust_shuffle_pack_peers")
+
+    def partition_histogram(self, dev_hist_ptr):
+        """adds this device's keys to a uint64[PARTITION_BINS] histogram in device memory"""
+        self._check(self._L.locust_partition_histogram(self._h, dev_hist_ptr), "locust_partition_histogram")
+
+    def partition_by_range(self, dev_hist_ptr, nparts):
+        """from the histogram summed over all ranks: later shuffle calls split by key range (0 parts = by hash)"""
+        self._check(self._L.locust_partition_by_range(self._h, dev_hist_ptr, nparts), "locust_partition_by_range")
+
+    def result_part_bytes(self):
+        n = ctypes.c_uint64()
+        self._check(self._L.locust_result_part_bytes(self._h, ctypes.byref(n)), "locust_result_part_bytes")
+        return n.value
+
+    def result_part_pack(self, dev_out_ptr):
+        self._check(self._L.locust_result_part_pack(self._h, dev_out_ptr), "locust_result_part_pack")
+
+    def result_concat(self, dev_part_ptrs, n_keys, blob_bytes, totals, keepalive=None):
+        if keepalive is not None:
+            self._keep.append(keepalive)
+        k = len(dev_part_ptrs)
+        u64s = ctypes.c_uint64 * k
+        self._check(self._L.locust_result_concat(self._h, k, (ctypes.c_void_p * k)(*dev_part_ptrs), u64s(*n_keys),
+                                                 u64s(*blob_bytes), u64s(*totals)), "locust_result_concat")
 
     def shuffle_begin_merge(self):
         self._check(self._L.locust_shuffle_begin_merge(self._h), "locust_shuffle_begin_merge")

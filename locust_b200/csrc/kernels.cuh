@@ -124,20 +124,27 @@ int launch_exclusive_scan_u64(const unsigned long long *in, unsigned long long *
 // when packed straight into a peer's slot).
 // part_counts: 2 * nparts scalars (short records, long bytes per part).
 int launch_shuffle_count(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
-                         const Counters *ctr, uint32_t nparts, unsigned long long *part_counts, int num_sms,
-                         cudaStream_t st);
-// part_offsets: nparts byte offsets into out; part_cursors: 2 * nparts scalars, zeroed by the caller
+                         const Counters *ctr, uint32_t nparts, const uint8_t *partmap, unsigned long long *part_counts,
+                         int num_sms, cudaStream_t st);
 int launch_shuffle_pack(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
-                        const Counters *ctr, uint32_t nparts, uint8_t *out, const unsigned long long *part_offsets,
-                        const unsigned long long *part_counts, unsigned long long *part_cursors, int num_sms,
-                        cudaStream_t st);
-// pack + send in one kernel: part q goes to dev_dst[q] (a slot in a peer's receive buffer);
-// part_cursors: 2 * nparts scalars, zeroed by the caller; *xflag |= 1 when something did not fit
+                        const Counters *ctr, uint32_t nparts, const uint8_t *partmap, uint8_t *out,
+                        const unsigned long long *part_offsets, const unsigned long long *part_counts,
+                        unsigned long long *part_cursors, int num_sms, cudaStream_t st);
 int launch_shuffle_pack_peers(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
-                              const Counters *ctr, uint32_t nparts, uint8_t *const *dev_dst, uint64_t short_cap,
-                              uint64_t long_room, unsigned long long *part_cursors, uint32_t *xflag, int num_sms,
-                              cudaStream_t st);
-// adds one received part to the table / long list of p
+                              const Counters *ctr, uint32_t nparts, const uint8_t *partmap, uint8_t *const *dev_dst,
+                              uint64_t short_cap, uint64_t long_room, unsigned long long *part_cursors, uint32_t *xflag,
+                              int num_sms, cudaStream_t st);
+// ordered shuffle: histogram of the keys' first two bytes (65 536 bins), bin -> part map
+int launch_partition_hist(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
+                          const Counters *ctr, unsigned long long *hist, int num_sms, cudaStream_t st);
+int launch_partition_map(const unsigned long long *hist, uint32_t nparts, uint8_t *partmap, cudaStream_t st);
+// a sorted result as one part {header, offsets, counts, vals, key bytes}; appending parts to a result
+int launch_result_pack(ReduceBufs red, const Counters *ctr, uint8_t *out, uint64_t n_hint, int num_sms, cudaStream_t st);
+int launch_result_header(const Counters *ctr, unsigned long long *dev_hdr, cudaStream_t st);
+int launch_result_push(ReduceBufs red, const unsigned long long *headers, uint32_t rank, uint32_t world, uint8_t *dst,
+                       uint64_t dst_bytes, uint64_t n_hint, int num_sms, cudaStream_t st);
+int launch_result_append(ReduceBufs red, const uint8_t *part, uint64_t n_base, uint64_t blob_base, uint64_t total_base,
+                         uint64_t n_hint, int num_sms, cudaStream_t st);
 int launch_shuffle_merge(const uint8_t *part, uint64_t nbytes, MapParams p, int num_sms, cudaStream_t st);
 
 }  // namespace locust

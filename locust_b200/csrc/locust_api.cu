@@ -70,6 +70,8 @@ struct locust_ctx {
     unsigned long long *part_dev = nullptr;  uint32_t part_cap = 0;
     std::vector<unsigned long long> part_host, part_off_host;
     uint32_t part_n = 0;
+    uint8_t *partmap = nullptr;              // ordered shuffle: first two key bytes -> part (65 536 entries)
+    uint32_t partmap_n = 0;                  // parts the map was built for; 0 = shuffle by hash
     // direct exchange: overflow flag of pack_peers (device + pinned mirror), receive buffers we own
     uint32_t *xflag = nullptr, *h_xflag = nullptr;
     std::vector<void *> exchange_bufs;
@@ -412,7 +414,7 @@ int locust_destroy(locust_ctx *c) {
     cudaFree(c->table); cudaFree(c->long_list); cudaFree(c->ctr);
     free_record_buffers(c);
     cudaFree(c->sort.hist); cudaFree(c->sort.bases); cudaFree(c->sort.tickets);
-    cudaFree(c->line_off); cudaFree(c->d_text); cudaFree(c->part_dev); cudaFree(c->xflag);
+    cudaFree(c->line_off); cudaFree(c->d_text); cudaFree(c->part_dev); cudaFree(c->xflag); cudaFree(c->partmap);
     for (void *b : c->exchange_bufs) cudaFree(b);
     cudaFreeHost(c->h_xflag);
     cudaFreeHost(c->h_ctr); cudaFreeHost(c->h_blob); cudaFreeHost(c->h_offsets);
@@ -435,6 +437,7 @@ int locust_reset(locust_ctx *c) {
     c->replayable = true;
     c->stage = 0;
     c->host_valid = false;
+    c->partmap_n = 0;
     for (auto &b : c->ev_set) b = false;
     c->launches = 0;
     c->err.clear();
@@ -643,6 +646,7 @@ int locust_map_intermediate(locust_ctx *c, const char *text, uint64_t nbytes) {
 }
 
 // ---- multi-GPU shuffle ------------------------------------------------------------------
+static const uint8_t *part_map_for(const locust_ctx *c) { return c->partmap_n ? c->partmap : nullptr; }
 static uint64_t part_bytes(uint64_t n_short, uint64_t long_bytes) {
     return (32ull + 32ull * n_short + long_bytes + 31ull) & ~31ull;
 }
@@ -651,6 +655,8 @@ int locust_shuffle_sizes(locust_ctx *c, uint32_t nparts, uint64_t *bytes_per_par
     if (!c || !bytes_per_part || nparts == 0) return LOCUST_E_ARG;
     if (nparts > 256) return fail(c, LOCUST_E_ARG, "locust_shuffle_sizes: at most 256 parts");
     if (c->stage != 0) return fail(c, LOCUST_E_STATE, "locust_shuffle_sizes after locust_process");
+    if (c->partmap_n && c->partmap_n != nparts)
+        return fail(c, LOCUST_E_STATE, "locust_shuffle_sizes: the key ranges were built for a different number of parts");
     CU(cudaSetDevice(c->device));
     if (!c->cleared) {            // nothing mapped on this rank: an empty job still takes part in the exchange
         CU(cudaEventRecord(c->ev[0], c->stream)); c->ev_set[0] = true;
@@ -671,7 +677,7 @@ int locust_shuffle_sizes(locust_ctx *c, uint32_t nparts, uint64_t *bytes_per_par
     for (int attempt = 0;; ++attempt) {
         CU(cudaMemsetAsync(c->part_dev, 0, 4ull * nparts * sizeof(unsigned long long), c->stream));
         c->launches += (uint64_t)launch_shuffle_count(c->table, c->slots, c->long_list, c->long_cap, c->ctr, nparts,
-                                                      c->part_dev, c->num_sms, c->stream);
+                                                      part_map_for(c), c->part_dev, c->num_sms, c->stream);
         CU(cudaGetLastError());
         CU(cudaMemcpyAsync(c->part_host.data(), c->part_dev, 2ull * nparts * sizeof(unsigned long long),
                            cudaMemcpyDeviceToHost, c->stream));
@@ -697,7 +703,7 @@ int locust_shuffle_pack(locust_ctx *c, uint32_t nparts, void *dev_out, const uin
     CU(cudaMemcpyAsync(c->part_dev + 4ull * nparts, c->part_off_host.data(), nparts * sizeof(unsigned long long),
                        cudaMemcpyHostToDevice, c->stream));
     c->launches += (uint64_t)launch_shuffle_pack(c->table, c->slots, c->long_list, c->long_cap, c->ctr, nparts,
-                                                 static_cast<uint8_t *>(dev_out), c->part_dev + 4ull * nparts, c->part_dev,
+                                                 part_map_for(c), static_cast<uint8_t *>(dev_out), c->part_dev + 4ull * nparts, c->part_dev,
                                                  c->part_dev + 2ull * nparts, c->num_sms, c->stream);
     CU(cudaGetLastError());
     return LOCUST_OK;      // (the offsets came from pageable memory: that copy was staged before it returned)
@@ -748,6 +754,8 @@ int locust_shuffle_pack_peers(locust_ctx *c, uint32_t nparts, void *const *dst_s
     if (slot_bytes % 32 || slot_bytes < 32 + 32 * short_cap)
         return fail(c, LOCUST_E_ARG, "locust_shuffle_pack_peers: slot_bytes must be a multiple of 32 and hold short_cap records");
     if (c->stage != 0) return fail(c, LOCUST_E_STATE, "locust_shuffle_pack_peers after locust_process");
+    if (c->partmap_n && c->partmap_n != nparts)
+        return fail(c, LOCUST_E_STATE, "locust_shuffle_pack_peers: the key ranges were built for a different number of parts");
     CU(cudaSetDevice(c->device));
     if (!c->cleared) {
         CU(cudaEventRecord(c->ev[0], c->stream)); c->ev_set[0] = true;
@@ -771,11 +779,101 @@ int locust_shuffle_pack_peers(locust_ctx *c, uint32_t nparts, void *const *dst_s
     CU(cudaMemcpyAsync(c->part_dev + 4ull * nparts, c->part_off_host.data(), nparts * sizeof(unsigned long long),
                        cudaMemcpyHostToDevice, c->stream));
     c->launches += (uint64_t)launch_shuffle_pack_peers(
-        c->table, c->slots, c->long_list, c->long_cap, c->ctr, nparts,
+        c->table, c->slots, c->long_list, c->long_cap, c->ctr, nparts, part_map_for(c),
         reinterpret_cast<uint8_t *const *>(c->part_dev + 4ull * nparts), short_cap, slot_bytes - 32 - 32 * short_cap,
         c->part_dev + 2ull * nparts, c->xflag, c->num_sms, c->stream);
     CU(cudaGetLastError());
     c->replayable = false;      // a MAP overflow can no longer be repaired by redoing MAP: the parts are gone
+    return LOCUST_OK;
+}
+
+// ---- ordered shuffle: parts are key ranges, so each rank's sorted result is one slice of the whole ----
+int locust_partition_histogram(locust_ctx *c, void *dev_hist) {
+    if (!c || !dev_hist) return LOCUST_E_ARG;
+    if (c->stage != 0) return fail(c, LOCUST_E_STATE, "locust_partition_histogram after locust_process");
+    CU(cudaSetDevice(c->device));
+    if (!c->cleared) {            // nothing mapped on this rank: it still takes part with an empty table
+        CU(cudaEventRecord(c->ev[0], c->stream)); c->ev_set[0] = true;
+        int rc0 = clear_job(c);
+        if (rc0) return rc0;
+        CU(cudaEventRecord(c->ev[1], c->stream)); c->ev_set[1] = true;
+    }
+    if (!c->ev_set[6]) { CU(cudaEventRecord(c->ev[6], c->stream)); c->ev_set[6] = true; }
+    c->launches += (uint64_t)launch_partition_hist(c->table, c->slots, c->long_list, c->long_cap, c->ctr,
+                                                   static_cast<unsigned long long *>(dev_hist), c->num_sms, c->stream);
+    CU(cudaGetLastError());
+    return LOCUST_OK;
+}
+
+int locust_partition_by_range(locust_ctx *c, const void *dev_hist, uint32_t nparts) {
+    if (!c) return LOCUST_E_ARG;
+    if (c->stage != 0) return fail(c, LOCUST_E_STATE, "locust_partition_by_range after locust_process");
+    if (nparts == 0) { c->partmap_n = 0; return LOCUST_OK; }       // back to the hash shuffle
+    if (!dev_hist) return LOCUST_E_ARG;
+    if (nparts > 256) return fail(c, LOCUST_E_ARG, "locust_partition_by_range: at most 256 parts");
+    CU(cudaSetDevice(c->device));
+    if (!c->partmap) CU(dalloc(&c->partmap, (uint64_t)LOCUST_PARTITION_BINS));
+    c->launches += (uint64_t)launch_partition_map(static_cast<const unsigned long long *>(dev_hist), nparts, c->partmap, c->stream);
+    CU(cudaGetLastError());
+    c->partmap_n = nparts;
+    return LOCUST_OK;
+}
+
+static uint64_t result_part_bytes(uint64_t n, uint64_t blob) { return (32ull + 8ull * (n + 1) + 16ull * n + blob + 31ull) & ~31ull; }
+
+int locust_result_part_bytes(locust_ctx *c, uint64_t *bytes) {
+    if (!c || !bytes) return LOCUST_E_ARG;
+    if (c->stage != 2) return fail(c, LOCUST_E_STATE, "locust_result_part_bytes before locust_reduce");
+    *bytes = result_part_bytes(c->h_ctr->n_out, c->h_ctr->blob_bytes);
+    return LOCUST_OK;
+}
+
+int locust_result_part_pack(locust_ctx *c, void *dev_out) {
+    if (!c || !dev_out) return LOCUST_E_ARG;
+    if (c->stage != 2) return fail(c, LOCUST_E_STATE, "locust_result_part_pack before locust_reduce");
+    if (reinterpret_cast<uintptr_t>(dev_out) % 8) return fail(c, LOCUST_E_ARG, "locust_result_part_pack: dev_out must be 8-byte aligned");
+    CU(cudaSetDevice(c->device));
+    c->launches += (uint64_t)launch_result_pack(c->red, c->ctr, static_cast<uint8_t *>(dev_out), c->h_ctr->n_out + (c->h_ctr->blob_bytes >> 4),
+                                                c->num_sms, c->stream);
+    CU(cudaGetLastError());
+    return LOCUST_OK;
+}
+
+int locust_result_concat(locust_ctx *c, uint32_t nparts, const void *const *dev_parts, const uint64_t *n_keys,
+                         const uint64_t *blob_bytes, const uint64_t *totals) {
+    if (!c || !nparts || !dev_parts || !n_keys || !blob_bytes || !totals) return LOCUST_E_ARG;
+    if (c->stage != 2) return fail(c, LOCUST_E_STATE, "locust_result_concat before locust_reduce");
+    CU(cudaSetDevice(c->device));
+    uint64_t n = 0, blob = 0, total = 0;
+    for (uint32_t i = 0; i < nparts; ++i) {
+        if (!dev_parts[i] || reinterpret_cast<uintptr_t>(dev_parts[i]) % 8)
+            return fail(c, LOCUST_E_ARG, "locust_result_concat: parts must be non-NULL and 8-byte aligned");
+        n += n_keys[i]; blob += blob_bytes[i]; total += totals[i];
+    }
+    // room for the whole result: the arrays of REDUCE are replaced if the sum does not fit
+    if (n > c->rec.cap) {
+        CU(cudaStreamSynchronize(c->stream));
+        cudaFree(c->red.key_offsets); cudaFree(c->red.counts); cudaFree(c->red.vals);
+        c->red.key_offsets = nullptr; c->red.counts = nullptr; c->red.vals = nullptr;
+        CU(dalloc(&c->red.key_offsets, n + 1)); CU(dalloc(&c->red.counts, n)); CU(dalloc(&c->red.vals, n));
+    }
+    if (blob > c->red.blob_cap) {
+        CU(cudaStreamSynchronize(c->stream));
+        cudaFree(c->red.key_blob); c->red.key_blob = nullptr;
+        c->red.blob_cap = blob + 64;
+        CU(dalloc(&c->red.key_blob, c->red.blob_cap));
+    }
+    uint64_t nb = 0, bb = 0, tb = 0;
+    for (uint32_t i = 0; i < nparts; ++i) {
+        c->launches += (uint64_t)launch_result_append(c->red, static_cast<const uint8_t *>(dev_parts[i]), nb, bb, tb,
+                                                      n_keys[i] + (blob_bytes[i] >> 4), c->num_sms, c->stream);
+        nb += n_keys[i]; bb += blob_bytes[i]; tb += totals[i];
+    }
+    CU(cudaGetLastError());
+    c->h_ctr->n_out = n; c->h_ctr->blob_bytes = blob; c->h_ctr->total = total;
+    CU(cudaMemcpyAsync(&c->ctr->n_out, &c->h_ctr->n_out, 3 * sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->host_valid = false;
     return LOCUST_OK;
 }
 

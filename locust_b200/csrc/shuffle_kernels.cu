@@ -1,5 +1,7 @@
 // shuffle_kernels.cu -- packing of a device's partial (word, count) records into one
-// part per destination, destination = hash(word) % nparts.
+// part per destination.  Destination = hash(word) % nparts, or, for the ordered shuffle, the
+// key range the word falls in (partmap: first two key bytes -> part, built from an all-reduced
+// histogram so that ranges hold about the same number of keys and part p sorts before p + 1).
 //
 // Stands in for writeKeyIntValues -> /tmp/out.txt (MapReduce/src/main.cu:116-124,
 // :428-430): the reference hands partials to the reduce stage through a text file,
@@ -10,10 +12,17 @@
 
 namespace locust {
 
-LC_D uint32_t part_of_short(uint64_t k0, uint64_t k1, uint32_t nparts) {
+// bin of a key = its first two bytes, big endian (a one-byte key has 0 as its second byte), so
+// bins are ordered like the keys
+LC_D uint32_t bin_of_short(uint64_t k0) { return (uint32_t)((k0 & 0xFFull) << 8) | (uint32_t)((k0 >> 8) & 0xFFull); }
+LC_D uint32_t bin_of_long(const uint8_t *ptr) { return ((uint32_t)ptr[0] << 8) | (uint32_t)ptr[1]; }
+
+LC_D uint32_t part_of_short(uint64_t k0, uint64_t k1, uint32_t nparts, const uint8_t *__restrict__ partmap) {
+    if (partmap) return partmap[bin_of_short(k0)];
     return (uint32_t)(hash_key128(k0, k1) >> 32) % nparts;
 }
-LC_D uint32_t part_of_long(const uint8_t *ptr, uint64_t len, uint32_t nparts) {
+LC_D uint32_t part_of_long(const uint8_t *ptr, uint64_t len, uint32_t nparts, const uint8_t *__restrict__ partmap) {
+    if (partmap) return partmap[bin_of_long(ptr)];
     uint64_t h = 1469598103934665603ull;
     for (uint64_t i = 0; i < len; ++i) { h ^= ptr[i]; h *= 1099511628211ull; }
     return (uint32_t)(mix64(h) >> 32) % nparts;
@@ -28,6 +37,7 @@ constexpr uint32_t kMaxParts = 256;
 __global__ void __launch_bounds__(256) shuffle_count_kernel(const Slot *__restrict__ table, uint64_t slots,
                                                             const LongOcc *__restrict__ long_list, uint64_t long_cap,
                                                             const Counters *ctr, uint32_t nparts,
+                                                            const uint8_t *__restrict__ partmap,
                                                             unsigned long long *part_counts) {
     __shared__ unsigned long long sh[2 * kMaxParts];
     for (uint32_t i = threadIdx.x; i < 2 * nparts; i += blockDim.x) sh[i] = 0ull;
@@ -35,13 +45,13 @@ __global__ void __launch_bounds__(256) shuffle_count_kernel(const Slot *__restri
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < slots; i += stride) {
         const ulonglong2 k = *reinterpret_cast<const ulonglong2 *>(table + i);
-        if ((k.x | k.y) != 0ull) atomicAdd(&sh[part_of_short(k.x, k.y, nparts)], 1ull);
+        if ((k.x | k.y) != 0ull) atomicAdd(&sh[part_of_short(k.x, k.y, nparts, partmap)], 1ull);
     }
     unsigned long long nl = ctr->n_long;
     if (nl > long_cap) nl = long_cap;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nl; i += stride) {
         const LongOcc t = long_list[i];
-        atomicAdd(&sh[nparts + part_of_long(t.ptr, t.len, nparts)], long_record_bytes(t.len));
+        atomicAdd(&sh[nparts + part_of_long(t.ptr, t.len, nparts, partmap)], long_record_bytes(t.len));
     }
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < 2 * nparts; i += blockDim.x)
@@ -50,7 +60,8 @@ __global__ void __launch_bounds__(256) shuffle_count_kernel(const Slot *__restri
 
 __global__ void __launch_bounds__(256) shuffle_pack_kernel(const Slot *__restrict__ table, uint64_t slots,
                                                            const LongOcc *__restrict__ long_list, uint64_t long_cap,
-                                                           const Counters *ctr, uint32_t nparts, uint8_t *out,
+                                                           const Counters *ctr, uint32_t nparts,
+                                                           const uint8_t *__restrict__ partmap, uint8_t *out,
                                                            const unsigned long long *__restrict__ part_offsets,
                                                            const unsigned long long *__restrict__ part_counts,
                                                            unsigned long long *part_cursors) {
@@ -72,7 +83,7 @@ __global__ void __launch_bounds__(256) shuffle_pack_kernel(const Slot *__restric
         const bool occ = (v.x | v.y) != 0ull;
         uint32_t part = 0;
         unsigned long long local = 0;
-        if (occ) { part = part_of_short(v.x, v.y, nparts); local = atomicAdd(&sh_cnt[part], 1ull); }
+        if (occ) { part = part_of_short(v.x, v.y, nparts, partmap); local = atomicAdd(&sh_cnt[part], 1ull); }
         __syncthreads();
         for (uint32_t q = threadIdx.x; q < nparts; q += blockDim.x)
             sh_base[q] = sh_cnt[q] ? atomicAdd(&part_cursors[q], sh_cnt[q]) : 0ull;
@@ -88,7 +99,7 @@ __global__ void __launch_bounds__(256) shuffle_pack_kernel(const Slot *__restric
     if (nl > long_cap) nl = long_cap;
     for (uint64_t i = tid; i < nl; i += stride) {
         const LongOcc t = long_list[i];
-        const uint32_t part = part_of_long(t.ptr, t.len, nparts);
+        const uint32_t part = part_of_long(t.ptr, t.len, nparts, partmap);
         const unsigned long long at = atomicAdd(&part_cursors[nparts + part], long_record_bytes(t.len));
         uint8_t *dst = out + part_offsets[part] + 32ull + 32ull * part_counts[part] + at;
         reinterpret_cast<unsigned long long *>(dst)[0] = t.len;
@@ -108,7 +119,8 @@ __global__ void __launch_bounds__(256) shuffle_pack_kernel(const Slot *__restric
 __global__ void __launch_bounds__(256) shuffle_pack_peers_kernel(const Slot *__restrict__ table, uint64_t slots,
                                                                  const LongOcc *__restrict__ long_list,
                                                                  uint64_t long_cap, const Counters *ctr,
-                                                                 uint32_t nparts, uint8_t *const *__restrict__ dst,
+                                                                 uint32_t nparts, const uint8_t *__restrict__ partmap,
+                                                                 uint8_t *const *__restrict__ dst,
                                                                  uint64_t short_cap, uint64_t long_room,
                                                                  unsigned long long *part_cursors, uint32_t *xflag) {
     __shared__ unsigned long long sh_cnt[kMaxParts], sh_base[kMaxParts];
@@ -124,7 +136,7 @@ __global__ void __launch_bounds__(256) shuffle_pack_peers_kernel(const Slot *__r
         const bool occ = (v.x | v.y) != 0ull;
         uint32_t part = 0;
         unsigned long long local = 0;
-        if (occ) { part = part_of_short(v.x, v.y, nparts); local = atomicAdd(&sh_cnt[part], 1ull); }
+        if (occ) { part = part_of_short(v.x, v.y, nparts, partmap); local = atomicAdd(&sh_cnt[part], 1ull); }
         __syncthreads();
         for (uint32_t q = threadIdx.x; q < nparts; q += blockDim.x)
             sh_base[q] = sh_cnt[q] ? atomicAdd(&part_cursors[q], sh_cnt[q]) : 0ull;
@@ -140,7 +152,7 @@ __global__ void __launch_bounds__(256) shuffle_pack_peers_kernel(const Slot *__r
     if (nl > long_cap) nl = long_cap;
     for (uint64_t i = tid; i < nl; i += stride) {
         const LongOcc t = long_list[i];
-        const uint32_t part = part_of_long(t.ptr, t.len, nparts);
+        const uint32_t part = part_of_long(t.ptr, t.len, nparts, partmap);
         const uint64_t need = long_record_bytes(t.len);
         const unsigned long long at = atomicAdd(&part_cursors[nparts + part], need);
         if (at + need > long_room) { atomicOr(xflag, 1u); continue; }
@@ -180,30 +192,177 @@ static inline unsigned grid_for(uint64_t n, int num_sms) {
 }
 
 int launch_shuffle_count(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
-                         const Counters *ctr, uint32_t nparts, unsigned long long *part_counts, int num_sms,
-                         cudaStream_t st) {
+                         const Counters *ctr, uint32_t nparts, const uint8_t *partmap, unsigned long long *part_counts,
+                         int num_sms, cudaStream_t st) {
     shuffle_count_kernel<<<grid_for(slots, num_sms), 256, 0, st>>>(table, slots, long_list, long_cap, ctr, nparts,
-                                                                  part_counts);
+                                                                  partmap, part_counts);
     return 1;
 }
 
 int launch_shuffle_pack(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
-                        const Counters *ctr, uint32_t nparts, uint8_t *out, const unsigned long long *part_offsets,
-                        const unsigned long long *part_counts, unsigned long long *part_cursors, int num_sms,
-                        cudaStream_t st) {
-    shuffle_pack_kernel<<<grid_for(slots, num_sms), 256, 0, st>>>(table, slots, long_list, long_cap, ctr, nparts, out,
-                                                                 part_offsets, part_counts, part_cursors);
+                        const Counters *ctr, uint32_t nparts, const uint8_t *partmap, uint8_t *out,
+                        const unsigned long long *part_offsets, const unsigned long long *part_counts,
+                        unsigned long long *part_cursors, int num_sms, cudaStream_t st) {
+    shuffle_pack_kernel<<<grid_for(slots, num_sms), 256, 0, st>>>(table, slots, long_list, long_cap, ctr, nparts, partmap,
+                                                                 out, part_offsets, part_counts, part_cursors);
     return 1;
 }
 
 int launch_shuffle_pack_peers(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
-                              const Counters *ctr, uint32_t nparts, uint8_t *const *dev_dst, uint64_t short_cap,
-                              uint64_t long_room, unsigned long long *part_cursors, uint32_t *xflag, int num_sms,
-                              cudaStream_t st) {
+                              const Counters *ctr, uint32_t nparts, const uint8_t *partmap, uint8_t *const *dev_dst,
+                              uint64_t short_cap, uint64_t long_room, unsigned long long *part_cursors, uint32_t *xflag,
+                              int num_sms, cudaStream_t st) {
     shuffle_pack_peers_kernel<<<grid_for(slots, num_sms), 256, 0, st>>>(table, slots, long_list, long_cap, ctr, nparts,
-                                                                       dev_dst, short_cap, long_room, part_cursors, xflag);
+                                                                       partmap, dev_dst, short_cap, long_room,
+                                                                       part_cursors, xflag);
     shuffle_headers_kernel<<<(nparts + 255) / 256, 256, 0, st>>>(nparts, dev_dst, short_cap, long_room, part_cursors, ctr, xflag);
     return 2;
+}
+
+
+// ---- ordered shuffle: key histogram and range map ----------------------------------------------
+// hist[bin] += number of this device's keys whose first two bytes are `bin` (65 536 bins).
+__global__ void __launch_bounds__(256) partition_hist_kernel(const Slot *__restrict__ table, uint64_t slots,
+                                                             const LongOcc *__restrict__ long_list, uint64_t long_cap,
+                                                             const Counters *ctr, unsigned long long *hist) {
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < slots; i += stride) {
+        const ulonglong2 k = *reinterpret_cast<const ulonglong2 *>(table + i);
+        if ((k.x | k.y) != 0ull) atomicAdd(&hist[bin_of_short(k.x)], 1ull);
+    }
+    unsigned long long nl = ctr->n_long;
+    if (nl > long_cap) nl = long_cap;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nl; i += stride)
+        atomicAdd(&hist[bin_of_long(long_list[i].ptr)], 1ull);
+}
+
+// One block of 1024 threads, 64 consecutive bins each: bin b goes to part
+// floor(keys_before(b) * nparts / total), which is monotone in b, so part p holds a contiguous
+// key range below part p + 1's, and the ranges hold about total / nparts keys each (as far as
+// whole bins allow).  Every rank computes the same map from the same all-reduced histogram.
+__global__ void __launch_bounds__(1024) partition_map_kernel(const unsigned long long *__restrict__ hist, uint32_t nparts,
+                                                             uint8_t *partmap) {
+    __shared__ unsigned long long part_sum[1024];
+    const uint32_t t = threadIdx.x;
+    unsigned long long mine = 0;
+    for (uint32_t b = 0; b < 64; ++b) mine += hist[t * 64u + b];
+    part_sum[t] = mine;
+    __syncthreads();
+    for (uint32_t o = 1; o < 1024; o <<= 1) {          // inclusive scan (Hillis-Steele; once per job)
+        const unsigned long long v = t >= o ? part_sum[t - o] : 0ull;
+        __syncthreads();
+        part_sum[t] += v;
+        __syncthreads();
+    }
+    const unsigned long long total = part_sum[1023];
+    unsigned long long before = part_sum[t] - mine;
+    for (uint32_t b = 0; b < 64; ++b) {
+        uint32_t part = 0;
+        if (total) {
+            // before < total <= 2^64 / 256 in any job that fits a GPU, so the product cannot overflow
+            part = (uint32_t)(before * nparts / total);
+            if (part >= nparts) part = nparts - 1;
+        }
+        partmap[t * 64u + b] = (uint8_t)part;
+        before += hist[t * 64u + b];
+    }
+}
+
+int launch_partition_hist(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
+                          const Counters *ctr, unsigned long long *hist, int num_sms, cudaStream_t st) {
+    partition_hist_kernel<<<grid_for(slots, num_sms), 256, 0, st>>>(table, slots, long_list, long_cap, ctr, hist);
+    return 1;
+}
+int launch_partition_map(const unsigned long long *hist, uint32_t nparts, uint8_t *partmap, cudaStream_t st) {
+    partition_map_kernel<<<1, 1024, 0, st>>>(hist, nparts, partmap);
+    return 1;
+}
+
+// ---- a rank's sorted result as one movable part, and the concatenation of such parts -----------
+// Part: header {n, blob_bytes, total, part_bytes}, key_offsets[n + 1], counts[n], vals[n], key bytes.
+__global__ void __launch_bounds__(256) result_pack_kernel(ReduceBufs red, const Counters *ctr, uint8_t *out) {
+    const unsigned long long n = ctr->n_out, blob = ctr->blob_bytes;
+    unsigned long long *h = reinterpret_cast<unsigned long long *>(out);
+    unsigned long long *off = h + 4, *cnt = off + n + 1, *val = cnt + n;
+    uint8_t *kb = reinterpret_cast<uint8_t *>(val + n);
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x, tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid == 0) { h[0] = n; h[1] = blob; h[2] = ctr->total; h[3] = (32ull + 8ull * (n + 1) + 16ull * n + blob + 31ull) & ~31ull; }
+    for (uint64_t i = tid; i <= n; i += stride) off[i] = red.key_offsets[i];
+    for (uint64_t i = tid; i < n; i += stride) { cnt[i] = red.counts[i]; val[i] = red.vals[i]; }
+    for (uint64_t i = tid; i < blob; i += stride) kb[i] = red.key_blob[i];
+}
+
+// Appends one part behind `n_base` keys / `blob_base` key bytes / `total_base` occurrences.
+__global__ void __launch_bounds__(256) result_append_kernel(ReduceBufs red, const uint8_t *__restrict__ part,
+                                                            unsigned long long n_base, unsigned long long blob_base,
+                                                            unsigned long long total_base) {
+    const unsigned long long *h = reinterpret_cast<const unsigned long long *>(part);
+    const unsigned long long n = h[0], blob = h[1];
+    const unsigned long long *off = h + 4, *cnt = off + n + 1, *val = cnt + n;
+    const uint8_t *kb = reinterpret_cast<const uint8_t *>(val + n);
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x, tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (uint64_t i = tid; i <= n; i += stride) red.key_offsets[n_base + i] = off[i] + blob_base;
+    for (uint64_t i = tid; i < n; i += stride) {
+        red.counts[n_base + i] = cnt[i];
+        red.vals[n_base + i] = val[i] + total_base;
+    }
+    for (uint64_t i = tid; i < blob; i += stride) red.key_blob[blob_base + i] = kb[i];
+}
+
+// The same without the detour through a local part: with every rank's header {n, blob_bytes, total, .}
+// at hand (headers[4 * r ..]), rank `rank` writes its slice straight into its place inside ONE part
+// that holds the whole result -- `dst`, normally peer memory of the rank that wants the result.
+// Rank 0 also writes that part's header.  If the whole does not fit `dst_bytes` nothing but the
+// header is written; the reader refuses it by its size.
+__global__ void __launch_bounds__(256) result_header_kernel(const Counters *ctr, unsigned long long *h) {
+    const unsigned long long n = ctr->n_out, blob = ctr->blob_bytes;
+    h[0] = n; h[1] = blob; h[2] = ctr->total; h[3] = (32ull + 8ull * (n + 1) + 16ull * n + blob + 31ull) & ~31ull;
+}
+__global__ void __launch_bounds__(256) result_push_kernel(ReduceBufs red, const unsigned long long *__restrict__ headers,
+                                                          uint32_t rank, uint32_t world, uint8_t *dst, uint64_t dst_bytes) {
+    unsigned long long n_tot = 0, blob_tot = 0, total_tot = 0, n_base = 0, blob_base = 0, total_base = 0;
+    for (uint32_t r = 0; r < world; ++r) {
+        if (r == rank) { n_base = n_tot; blob_base = blob_tot; total_base = total_tot; }
+        n_tot += headers[4 * r]; blob_tot += headers[4 * r + 1]; total_tot += headers[4 * r + 2];
+    }
+    const unsigned long long n = headers[4 * rank], blob = headers[4 * rank + 1];
+    const unsigned long long bytes = (32ull + 8ull * (n_tot + 1) + 16ull * n_tot + blob_tot + 31ull) & ~31ull;
+    unsigned long long *h = reinterpret_cast<unsigned long long *>(dst);
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x, tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (rank == 0 && tid == 0) { h[0] = n_tot; h[1] = blob_tot; h[2] = total_tot; h[3] = bytes; }
+    if (bytes <= dst_bytes) {
+        unsigned long long *off = h + 4, *cnt = off + n_tot + 1, *val = cnt + n_tot;
+        uint8_t *kb = reinterpret_cast<uint8_t *>(val + n_tot);
+        // offsets [n_base, n_base + n) belong to this rank; the closing offset to the last rank
+        for (uint64_t i = tid; i < n; i += stride) {
+            off[n_base + i] = red.key_offsets[i] + blob_base;
+            cnt[n_base + i] = red.counts[i];
+            val[n_base + i] = red.vals[i] + total_base;
+        }
+        if (rank == world - 1 && tid == 0) off[n_tot] = blob_tot;
+        for (uint64_t i = tid; i < blob; i += stride) kb[blob_base + i] = red.key_blob[i];
+    }
+    __threadfence_system();
+}
+
+int launch_result_header(const Counters *ctr, unsigned long long *dev_hdr, cudaStream_t st) {
+    result_header_kernel<<<1, 1, 0, st>>>(ctr, dev_hdr);
+    return 1;
+}
+int launch_result_push(ReduceBufs red, const unsigned long long *headers, uint32_t rank, uint32_t world, uint8_t *dst,
+                       uint64_t dst_bytes, uint64_t n_hint, int num_sms, cudaStream_t st) {
+    result_push_kernel<<<grid_for(n_hint * 16 + 1024, num_sms), 256, 0, st>>>(red, headers, rank, world, dst, dst_bytes);
+    return 1;
+}
+
+int launch_result_pack(ReduceBufs red, const Counters *ctr, uint8_t *out, uint64_t n_hint, int num_sms, cudaStream_t st) {
+    result_pack_kernel<<<grid_for(n_hint * 16 + 1024, num_sms), 256, 0, st>>>(red, ctr, out);
+    return 1;
+}
+int launch_result_append(ReduceBufs red, const uint8_t *part, uint64_t n_base, uint64_t blob_base, uint64_t total_base,
+                         uint64_t n_hint, int num_sms, cudaStream_t st) {
+    result_append_kernel<<<grid_for(n_hint * 16 + 1024, num_sms), 256, 0, st>>>(red, part, n_base, blob_base, total_base);
+    return 1;
 }
 
 }  // namespace locust

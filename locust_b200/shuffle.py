@@ -14,6 +14,11 @@ command channel (Distributor/slave.py) -- with an all-to-all over NVLink:
     gather the partitions on rank 0       the same pack / exchange / merge with one destination
     process + reduce on rank 0            locust_process / locust_reduce  -> sorted result
 
+  ordered=True replaces the last three lines: the parts of the exchange are key ranges
+  (locust_partition_histogram, all-reduce, locust_partition_by_range), every rank runs process +
+  reduce on its own range, and rank 0 receives the sorted slices and puts them one after the
+  other (locust_result_part_pack / locust_result_concat) -- nobody sorts the whole result.
+
 torch.distributed is plumbing only; every byte of arithmetic happens in liblocust.so.  The class
 is written against a small backend interface so the exchange logic can be tested on CPU with
 gloo (tests/test_shuffle_host.py) without a GPU.
@@ -74,6 +79,26 @@ class GpuBackend:
     def reduce(self):
         self.wc.reduce()
 
+    # ordered shuffle
+    def histogram(self):
+        h = self.torch.zeros(65536, dtype=self.torch.int64, device=self.device)
+        self.wc.partition_histogram(h.data_ptr())
+        return h
+
+    def partition_by_range(self, hist, nparts):
+        self.wc.partition_by_range(hist.data_ptr(), nparts)
+
+    def result_part(self):
+        """(packed result of this rank as a uint8 tensor, its 4-word header as an int64 tensor)"""
+        nbytes = self.wc.result_part_bytes()
+        buf = self.alloc(nbytes)
+        self.wc.result_part_pack(buf.data_ptr())
+        return buf[:nbytes], buf[:32].view(self.torch.int64)
+
+    def result_concat(self, buf, offsets, headers):
+        self.wc.result_concat([buf.data_ptr() + o for o in offsets], [h[0] for h in headers], [h[1] for h in headers],
+                              [h[2] for h in headers], keepalive=buf)
+
 
 class PeerExchange:
     """Receive buffers for the fused pack + send path, mapped into every rank of one box.
@@ -129,10 +154,10 @@ class PeerExchange:
 
 class DistributedWordCount:
     """run(shard) on every rank; afterwards rank 0's backend holds the sorted result of the
-    whole input and the other ranks hold an empty one."""
+    whole input and the other ranks hold an empty one (ordered=True: the slice of their key range)."""
 
-    def __init__(self, backend, dist, group=None, peers=None):
-        self.b, self.dist, self.group, self.peers = backend, dist, group, peers
+    def __init__(self, backend, dist, group=None, peers=None, ordered=False):
+        self.b, self.dist, self.group, self.peers, self.ordered = backend, dist, group, peers, ordered
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
         self.last_shuffle_bytes = 0          # bytes this rank sent to other ranks in the hash shuffle
@@ -182,10 +207,41 @@ class DistributedWordCount:
         for s in range(nslots):
             wc.shuffle_merge(px.mine[which] + s * px.slot_bytes, px.slot_bytes)
 
+    def _gather_results(self):
+        """every rank's sorted slice goes to rank 0, which strings them together in rank order"""
+        b = self.b
+        part, header = b.result_part()
+        headers = b.sizes_tensor([0] * (4 * self.world))
+        self.dist.all_gather_into_tensor(headers, header, group=self.group)
+        headers = headers.tolist()
+        headers = [headers[4 * r:4 * r + 4] for r in range(self.world)]
+        sizes = [h[3] for h in headers]
+        recv_sizes = sizes if self.rank == 0 else [0] * self.world
+        send_sizes = [sizes[self.rank]] + [0] * (self.world - 1)
+        recvbuf = b.alloc(sum(recv_sizes))
+        self.dist.all_to_all_single(recvbuf[:sum(recv_sizes)], part, output_split_sizes=recv_sizes,
+                                    input_split_sizes=send_sizes, group=self.group)
+        if self.rank == 0:
+            offsets = [sum(sizes[:r]) for r in range(self.world)]
+            b.result_concat(recvbuf, offsets, headers)
+
     def run(self, shard):
         b = self.b
         b.reset()
         b.map(shard)
+        if self.world > 1 and self.ordered:
+            hist = b.histogram()
+            self.dist.all_reduce(hist, group=self.group)
+            b.partition_by_range(hist, self.world)
+            if self.peers is not None:
+                self._shuffle_peers(0, list(range(self.world)))
+            else:
+                sent = self._shuffle(self.world, list(range(self.world)))
+                self.last_shuffle_bytes = sum(s for r, s in enumerate(sent) if r != self.rank)
+            b.process()
+            b.reduce()
+            self._gather_results()
+            return self
         if self.world > 1 and self.peers is not None:
             self._shuffle_peers(0, list(range(self.world)))
             self._shuffle_peers(1, [0])

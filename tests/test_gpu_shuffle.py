@@ -193,3 +193,108 @@ def test_pack_straight_into_peer_slots(lb, P):
     finally:
         for c in ctx:
             c.close()
+
+
+def emulate_ordered(lb, data, P, **kw):
+    """the ordered shuffle over P emulated ranks: parts are key ranges, every rank sorts its own
+    range, rank 0 strings the slices together.  Returns rank 0's (keys, counts, vals) and the
+    per-rank slices [(keys, counts)]."""
+    dev = torch.frombuffer(bytearray(data) if data else bytearray(1), dtype=torch.uint8)[:len(data)].cuda()
+    shards = plan_shards(data, P)
+    ctx = [lb.WordCount(device=0, **kw) for _ in range(P)]
+    keep = []
+    try:
+        hist = torch.zeros(lb.PARTITION_BINS, dtype=torch.int64, device="cuda")
+        torch.cuda.synchronize()
+        for r, (lo, hi) in enumerate(shards):
+            ctx[r].reset()
+            ctx[r].map(dev[lo:hi])
+            ctx[r].partition_histogram(hist.data_ptr())        # every rank adds into the same array = the all-reduce
+        torch.cuda.synchronize()
+        for r in range(P):
+            ctx[r].partition_by_range(hist.data_ptr(), P)
+        inbox = [[] for _ in range(P)]
+        for s in range(P):
+            sizes = ctx[s].shuffle_sizes(P)
+            offs = [sum(sizes[:i]) for i in range(P)]
+            buf = torch.zeros(sum(sizes), dtype=torch.uint8, device="cuda")
+            torch.cuda.synchronize()
+            ctx[s].shuffle_pack(P, buf.data_ptr(), offs)
+            keep.append(buf)
+            for i in range(P):
+                inbox[i].append((buf, offs[i], sizes[i]))
+        slices, parts = [], []
+        for r in range(P):
+            ctx[r].shuffle_begin_merge()
+            for buf, o, x in inbox[r]:
+                ctx[r].shuffle_merge(buf.data_ptr() + o, x, keepalive=buf)
+            ctx[r].process()
+            ctx[r].reduce()
+            k, c, _ = ctx[r].result()
+            slices.append((k, c))
+            part = torch.zeros(ctx[r].result_part_bytes(), dtype=torch.uint8, device="cuda")
+            torch.cuda.synchronize()
+            ctx[r].result_part_pack(part.data_ptr())
+            parts.append(part)
+        torch.cuda.synchronize()
+        headers = [p[:32].view(torch.int64).tolist() for p in parts]
+        assert all(h[3] == p.numel() for h, p in zip(headers, parts))
+        ctx[0].result_concat([p.data_ptr() for p in parts], [h[0] for h in headers], [h[1] for h in headers],
+                             [h[2] for h in headers], keepalive=parts)
+        keys, counts, vals = ctx[0].result()
+        return keys, counts, vals, slices, ctx[0].stats()
+    finally:
+        for c in ctx:
+            c.close()
+
+
+@pytest.mark.parametrize("P", [1, 2, 3, 8])
+def test_ordered_shuffle_matches_the_oracle(lb, P):
+    from oracle import pyoracle
+    data = golden_input("hamlet") + golden_input("edge_long_tokens") + b" " + golden_input("rand_longtok_s5")
+    keys, counts, vals, slices, stats = emulate_ordered(lb, data, P, table_log2=14)
+    ref = pyoracle.wordcount(data)
+    assert keys == ref.keys and counts == ref.counts
+    assert vals == [sum(ref.counts[:i]) for i in range(len(ref.counts))]
+    assert stats["unique_keys"] == len(ref.keys) and stats["tokens"] == sum(ref.counts)
+    # slices are consecutive key ranges in rank order, and no rank got everything (hamlet has many first letters)
+    flat = [k for ks, _ in slices for k in ks]
+    assert flat == ref.keys
+    if P > 1:
+        assert max(len(ks) for ks, _ in slices) < len(ref.keys)
+
+
+def test_ordered_shuffle_every_first_byte_and_tiny_inputs(lb):
+    from oracle import pyoracle
+    rng = random.Random(11)
+    alphabet = [bytes([b]) for b in range(1, 256) if bytes([b]) not in b" ,.-;:'()\"\t\n"]
+    words = [b"".join(rng.choice(alphabet) for _ in range(rng.choice((1, 1, 2, 3, 9, 17, 40)))) for _ in range(3000)]
+    data = b" ".join(rng.choice(words) for _ in range(20000))
+    keys, counts, _, slices, _ = emulate_ordered(lb, data, 4, table_log2=13)
+    ref = pyoracle.wordcount(data)
+    assert keys == ref.keys and counts == ref.counts
+    assert [k for ks, _ in slices for k in ks] == ref.keys
+    # fewer keys than ranks, and no keys at all
+    for tiny in (b"b a", b"", b"same same same"):
+        keys, counts, _, _, _ = emulate_ordered(lb, tiny, 4, table_log2=10)
+        ref = pyoracle.wordcount(tiny)
+        assert keys == ref.keys and counts == ref.counts
+
+
+def test_range_parts_need_matching_nparts(lb):
+    c = lb.WordCount(device=0, table_log2=10)
+    try:
+        d = torch.frombuffer(bytearray(b"a b c d"), dtype=torch.uint8).cuda()
+        c.reset()
+        c.map(d)
+        hist = torch.zeros(lb.PARTITION_BINS, dtype=torch.int64, device="cuda")
+        torch.cuda.synchronize()
+        c.partition_histogram(hist.data_ptr())
+        c.partition_by_range(hist.data_ptr(), 4)
+        with pytest.raises(lb.LocustError):
+            c.shuffle_sizes(2)
+        assert len(c.shuffle_sizes(4)) == 4
+        c.partition_by_range(0, 0)                 # back to hash parts
+        assert len(c.shuffle_sizes(2)) == 2
+    finally:
+        c.close()

@@ -39,6 +39,7 @@ class PyBackend:
     def __init__(self):
         self.counts = {}
         self.result = None
+        self.partmap = None
 
     def alloc(self, nbytes):
         return torch.zeros(max(int(nbytes), 32), dtype=torch.uint8)
@@ -47,7 +48,7 @@ class PyBackend:
         return torch.tensor(values, dtype=torch.int64)
 
     def reset(self):
-        self.counts, self.result = {}, None
+        self.counts, self.result, self.partmap = {}, None, None
 
     def map(self, buf):
         for t in re.split(b"[" + re.escape(DELIMS) + b"]+", bytes(buf)):
@@ -57,8 +58,50 @@ class PyBackend:
     def _parts(self, nparts):
         parts = [([], []) for _ in range(nparts)]
         for k, c in self.counts.items():
-            parts[zlib.crc32(k) % nparts][0 if len(k) <= 16 else 1].append((k, c))
+            dest = self.partmap[self._bin(k)] if self.partmap is not None else zlib.crc32(k) % nparts
+            parts[dest][0 if len(k) <= 16 else 1].append((k, c))
         return parts
+
+    # ordered shuffle: the same arithmetic as partition_hist_kernel / partition_map_kernel
+    @staticmethod
+    def _bin(k):
+        return (k[0] << 8) | (k[1] if len(k) > 1 else 0)
+
+    def histogram(self):
+        h = torch.zeros(65536, dtype=torch.int64)
+        for k in self.counts:
+            h[self._bin(k)] += 1
+        return h
+
+    def partition_by_range(self, hist, nparts):
+        hist = hist.tolist()
+        total, before, self.partmap = sum(hist), 0, []
+        for v in hist:
+            self.partmap.append(min(before * nparts // total, nparts - 1) if total else 0)
+            before += v
+
+    def result_part(self):
+        keys = [k for k, _ in self.result]
+        counts = [c for _, c in self.result]
+        n, blob = len(keys), b"".join(keys)
+        offs = [sum(len(k) for k in keys[:i]) for i in range(n + 1)]
+        vals = [sum(counts[:i]) for i in range(n)]
+        nbytes = (32 + 8 * (n + 1) + 16 * n + len(blob) + 31) // 32 * 32
+        raw = struct.pack("<4Q", n, len(blob), sum(counts), nbytes) + struct.pack("<%dQ" % (3 * n + 1), *offs, *counts, *vals) + blob
+        t = torch.tensor(list(raw.ljust(nbytes, b"\0")), dtype=torch.uint8)
+        return t, t[:32].view(torch.int64)
+
+    def result_concat(self, buf, offsets, headers):
+        raw = bytes(buf.numpy())
+        self.result, total_before = [], 0
+        for off, (n, blob_bytes, total, nbytes) in zip(offsets, headers):
+            assert struct.unpack_from("<4Q", raw, off) == (n, blob_bytes, total, nbytes)
+            words = struct.unpack_from("<%dQ" % (3 * n + 1), raw, off + 32)
+            offs, counts, vals = words[:n + 1], words[n + 1:2 * n + 1], words[2 * n + 1:]
+            blob = raw[off + 32 + 8 * (3 * n + 1):][:blob_bytes]
+            assert list(vals) == [sum(counts[:i]) for i in range(n)] and sum(counts) == total
+            self.result += [(blob[offs[i]:offs[i + 1]], counts[i]) for i in range(n)]
+            total_before += total
 
     @staticmethod
     def _long_bytes(longs):
@@ -106,20 +149,26 @@ class PyBackend:
         self.result = sorted(self.counts.items())
 
 
-def _worker(rank, world, port, data, out_path):
+def _worker(rank, world, port, data, out_path, ordered=False):
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         lo, hi = plan_shards(data, world)[rank]
-        job = DistributedWordCount(PyBackend(), dist)
+        job = DistributedWordCount(PyBackend(), dist, ordered=ordered)
         for _ in range(2):                       # twice: the job object is reusable
             job.run(data[lo:hi])
         if rank == 0:
             with open(out_path, "wb") as f:
                 for k, c in job.b.result:
                     f.write(k + b"\t%d\n" % c)
+        elif ordered:
+            # this rank kept the slice of its key range: sorted, and a proper part of the whole
+            keys = [k for k, _ in job.b.result]
+            assert keys == sorted(keys) and len(set(keys)) == len(keys)
+            with open(out_path + ".%d" % rank, "wb") as f:
+                f.write(b"\n".join(keys))
         else:
             assert job.b.result == []            # everything was gathered on rank 0
         assert job.last_shuffle_bytes % 32 == 0
@@ -138,3 +187,24 @@ def test_two_rank_exchange_matches_the_oracle(tmp_path, world):
     with open(out, "rb") as f:
         got = f.read()
     assert got == pyoracle.wordcount(data).tsv
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_ordered_exchange_matches_the_oracle(tmp_path, world):
+    """ordered=True: parts are key ranges, every rank sorts its own, rank 0 concatenates."""
+    import torch.multiprocessing as mp
+    from oracle import pyoracle
+    data = golden_input("hamlet") + golden_input("edge_long_tokens") + b"\n" + golden_input("rand_longtok_s5")
+    out = str(tmp_path / "result.tsv")
+    port = 29500 + (os.getpid() % 2000) + 10 + world
+    mp.spawn(_worker, args=(world, port, data, out, True), nprocs=world, join=True)
+    ref = pyoracle.wordcount(data)
+    with open(out, "rb") as f:
+        assert f.read() == ref.tsv
+    # the slices the other ranks kept are consecutive tails of the sorted key list
+    tail = []
+    for r in range(1, world):
+        with open(out + ".%d" % r, "rb") as f:
+            got = f.read()
+        tail += got.split(b"\n") if got else []
+    assert tail == ref.keys[len(ref.keys) - len(tail):] and 0 < len(tail) < len(ref.keys)
