@@ -210,7 +210,14 @@ int locust_shuffle_merge(locust_ctx *ctx, const void *dev_records, uint64_t nbyt
  *     {n, key_bytes, total, part_bytes | key_offsets[n+1] | counts[n] | vals[n] | key bytes};
  *   locust_result_concat, on the rank that wants the whole result, replaces its own result by
  *     the given parts in order (its own part included), rebasing offsets and vals.  n_keys,
- *     blob_bytes, totals: the first three header words of each part, host arrays. */
+ *     blob_bytes, totals: the first three header words of each part, host arrays.
+ *
+ * On one box the parts need not be sent by a collective: the receiver owns a buffer of one
+ * slot per rank (locust_exchange_alloc, mapped by the others with locust_ipc_*), every rank
+ * packs its part straight into its slot over NVLink (locust_result_part_pack with the slot's
+ * peer address; a rank whose part is larger than the slot writes only its header there,
+ * locust_result_header), and after a barrier the receiver strings the slots together with
+ * locust_result_adopt_slots (LOCUST_E_CAPACITY if a part did not fit). */
 #define LOCUST_PARTITION_BINS 65536u
 int locust_partition_histogram(locust_ctx *ctx, void *dev_hist);
 int locust_partition_by_range(locust_ctx *ctx, const void *dev_hist, uint32_t nparts);
@@ -218,6 +225,8 @@ int locust_result_part_bytes(locust_ctx *ctx, uint64_t *bytes);
 int locust_result_part_pack(locust_ctx *ctx, void *dev_out);
 int locust_result_concat(locust_ctx *ctx, uint32_t nparts, const void *const *dev_parts, const uint64_t *n_keys,
                          const uint64_t *blob_bytes, const uint64_t *totals);
+int locust_result_header(locust_ctx *ctx, void *dev_header);
+int locust_result_adopt_slots(locust_ctx *ctx, const void *dev_slots, uint64_t slot_bytes, uint32_t nslots);
 
 /* ---- for callers that cannot allocate ------------------------------------------
  * No counterpart in the reference (its main() allocates freely, main.cu:393,:402,:451).

@@ -28,6 +28,7 @@ EXPORTS = [
     "locust_map_intermediate", "locust_exchange_alloc", "locust_ipc_export", "locust_ipc_open", "locust_ipc_close",
     "locust_shuffle_pack_peers", "locust_partition_histogram", "locust_partition_by_range",
     "locust_result_part_bytes", "locust_result_part_pack", "locust_result_concat",
+    "locust_result_header", "locust_result_adopt_slots",
 ]
 PARTITION_BINS = 65536
 STATIC_MAX_KEYS = 16384
@@ -93,6 +94,8 @@ def load():
     L.locust_result_part_bytes.argtypes = [vp, pp(u64)]
     L.locust_result_part_pack.argtypes = [vp, vp]
     L.locust_result_concat.argtypes = [vp, u32, pp(vp), pp(u64), pp(u64), pp(u64)]
+    L.locust_result_header.argtypes = [vp, vp]
+    L.locust_result_adopt_slots.argtypes = [vp, vp, u64, u32]
     _lib = L
     return L
 
@@ -313,6 +316,13 @@ class WordCount:
         u64s = ctypes.c_uint64 * k
         self._check(self._L.locust_result_concat(self._h, k, (ctypes.c_void_p * k)(*dev_part_ptrs), u64s(*n_keys),
                                                  u64s(*blob_bytes), u64s(*totals)), "locust_result_concat")
+
+    def result_header(self, dev_header_ptr):
+        self._check(self._L.locust_result_header(self._h, dev_header_ptr), "locust_result_header")
+
+    def result_adopt_slots(self, dev_slots_ptr, slot_bytes, nslots):
+        self._check(self._L.locust_result_adopt_slots(self._h, dev_slots_ptr, slot_bytes, nslots),
+                    "locust_result_adopt_slots")
 
     def shuffle_begin_merge(self):
         self._check(self._L.locust_shuffle_begin_merge(self._h), "locust_shuffle_begin_merge")

@@ -141,8 +141,6 @@ int launch_partition_map(const unsigned long long *hist, uint32_t nparts, uint8_
 // a sorted result as one part {header, offsets, counts, vals, key bytes}; appending parts to a result
 int launch_result_pack(ReduceBufs red, const Counters *ctr, uint8_t *out, uint64_t n_hint, int num_sms, cudaStream_t st);
 int launch_result_header(const Counters *ctr, unsigned long long *dev_hdr, cudaStream_t st);
-int launch_result_push(ReduceBufs red, const unsigned long long *headers, uint32_t rank, uint32_t world, uint8_t *dst,
-                       uint64_t dst_bytes, uint64_t n_hint, int num_sms, cudaStream_t st);
 int launch_result_append(ReduceBufs red, const uint8_t *part, uint64_t n_base, uint64_t blob_base, uint64_t total_base,
                          uint64_t n_hint, int num_sms, cudaStream_t st);
 int launch_shuffle_merge(const uint8_t *part, uint64_t nbytes, MapParams p, int num_sms, cudaStream_t st);

@@ -877,6 +877,38 @@ int locust_result_concat(locust_ctx *c, uint32_t nparts, const void *const *dev_
     return LOCUST_OK;
 }
 
+int locust_result_header(locust_ctx *c, void *dev_header) {
+    if (!c || !dev_header) return LOCUST_E_ARG;
+    if (c->stage != 2) return fail(c, LOCUST_E_STATE, "locust_result_header before locust_reduce");
+    if (reinterpret_cast<uintptr_t>(dev_header) % 8) return fail(c, LOCUST_E_ARG, "locust_result_header: dev_header must be 8-byte aligned");
+    CU(cudaSetDevice(c->device));
+    c->launches += (uint64_t)launch_result_header(c->ctr, static_cast<unsigned long long *>(dev_header), c->stream);
+    CU(cudaGetLastError());
+    return LOCUST_OK;
+}
+
+int locust_result_adopt_slots(locust_ctx *c, const void *dev_slots, uint64_t slot_bytes, uint32_t nslots) {
+    if (!c || !dev_slots || nslots == 0 || nslots > 256) return LOCUST_E_ARG;
+    if (c->stage != 2) return fail(c, LOCUST_E_STATE, "locust_result_adopt_slots before locust_reduce");
+    if (slot_bytes < 64 || slot_bytes % 32 || reinterpret_cast<uintptr_t>(dev_slots) % 8)
+        return fail(c, LOCUST_E_ARG, "locust_result_adopt_slots: slots are multiples of 32 bytes, 8-byte aligned");
+    CU(cudaSetDevice(c->device));
+    uint64_t h[256 * 4];
+    CU(cudaMemcpy2DAsync(h, 32, dev_slots, slot_bytes, 32, nslots, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    const void *parts[256];
+    uint64_t n[256], blob[256], total[256];
+    for (uint32_t i = 0; i < nslots; ++i) {
+        if (h[4 * i + 3] > slot_bytes)
+            return fail(c, LOCUST_E_CAPACITY, "locust_result_adopt_slots: a rank's slice did not fit its slot (raise the slot size)");
+        if (h[4 * i + 3] != result_part_bytes(h[4 * i], h[4 * i + 1]))
+            return fail(c, LOCUST_E_STATE, "locust_result_adopt_slots: a slot does not hold a packed result");
+        parts[i] = static_cast<const uint8_t *>(dev_slots) + (uint64_t)i * slot_bytes;
+        n[i] = h[4 * i]; blob[i] = h[4 * i + 1]; total[i] = h[4 * i + 2];
+    }
+    return locust_result_concat(c, nslots, parts, n, blob, total);
+}
+
 int locust_shuffle_begin_merge(locust_ctx *c) {
     if (!c) return LOCUST_E_ARG;
     if (c->stage != 0) return fail(c, LOCUST_E_STATE, "locust_shuffle_begin_merge after locust_process");

@@ -236,35 +236,43 @@ __global__ void __launch_bounds__(256) partition_hist_kernel(const Slot *__restr
         atomicAdd(&hist[bin_of_long(long_list[i].ptr)], 1ull);
 }
 
-// One block of 1024 threads, 64 consecutive bins each: bin b goes to part
-// floor(keys_before(b) * nparts / total), which is monotone in b, so part p holds a contiguous
-// key range below part p + 1's, and the ranges hold about total / nparts keys each (as far as
-// whole bins allow).  Every rank computes the same map from the same all-reduced histogram.
+// One block of 32 warps, 2048 consecutive bins per warp, read 32 at a time (coalesced): bin b
+// goes to part floor(keys_before(b) * nparts / total), which is monotone in b, so part p holds
+// a contiguous key range below part p + 1's, and the ranges hold about total / nparts keys each
+// (as far as whole bins allow).  Every rank computes the same map from the same all-reduced
+// histogram.
 __global__ void __launch_bounds__(1024) partition_map_kernel(const unsigned long long *__restrict__ hist, uint32_t nparts,
                                                              uint8_t *partmap) {
-    __shared__ unsigned long long part_sum[1024];
-    const uint32_t t = threadIdx.x;
-    unsigned long long mine = 0;
-    for (uint32_t b = 0; b < 64; ++b) mine += hist[t * 64u + b];
-    part_sum[t] = mine;
+    __shared__ unsigned long long warp_sum[32];
+    const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
+    const unsigned long long *mine = hist + w * 2048u;
+    unsigned long long acc = 0;
+#pragma unroll 16
+    for (uint32_t j = 0; j < 64; ++j) acc += mine[j * 32u + lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+    if (lane == 0) warp_sum[w] = acc;
     __syncthreads();
-    for (uint32_t o = 1; o < 1024; o <<= 1) {          // inclusive scan (Hillis-Steele; once per job)
-        const unsigned long long v = t >= o ? part_sum[t - o] : 0ull;
-        __syncthreads();
-        part_sum[t] += v;
-        __syncthreads();
-    }
-    const unsigned long long total = part_sum[1023];
-    unsigned long long before = part_sum[t] - mine;
-    for (uint32_t b = 0; b < 64; ++b) {
+    unsigned long long total = 0, carry = 0;
+    for (uint32_t k = 0; k < 32; ++k) { if (k == w) carry = total; total += warp_sum[k]; }
+#pragma unroll 4
+    for (uint32_t j = 0; j < 64; ++j) {
+        const unsigned long long v = mine[j * 32u + lane];
+        unsigned long long incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= (uint32_t)o) incl += y;
+        }
+        const unsigned long long before = carry + incl - v;
         uint32_t part = 0;
         if (total) {
             // before < total <= 2^64 / 256 in any job that fits a GPU, so the product cannot overflow
             part = (uint32_t)(before * nparts / total);
             if (part >= nparts) part = nparts - 1;
         }
-        partmap[t * 64u + b] = (uint8_t)part;
-        before += hist[t * 64u + b];
+        partmap[w * 2048u + j * 32u + lane] = (uint8_t)part;
+        carry += __shfl_sync(0xFFFFFFFFu, incl, 31);
     }
 }
 
@@ -290,6 +298,7 @@ __global__ void __launch_bounds__(256) result_pack_kernel(ReduceBufs red, const 
     for (uint64_t i = tid; i <= n; i += stride) off[i] = red.key_offsets[i];
     for (uint64_t i = tid; i < n; i += stride) { cnt[i] = red.counts[i]; val[i] = red.vals[i]; }
     for (uint64_t i = tid; i < blob; i += stride) kb[i] = red.key_blob[i];
+    __threadfence_system();          // `out` may be a peer's memory
 }
 
 // Appends one part behind `n_base` keys / `blob_base` key bytes / `total_base` occurrences.
@@ -309,49 +318,15 @@ __global__ void __launch_bounds__(256) result_append_kernel(ReduceBufs red, cons
     for (uint64_t i = tid; i < blob; i += stride) red.key_blob[blob_base + i] = kb[i];
 }
 
-// The same without the detour through a local part: with every rank's header {n, blob_bytes, total, .}
-// at hand (headers[4 * r ..]), rank `rank` writes its slice straight into its place inside ONE part
-// that holds the whole result -- `dst`, normally peer memory of the rank that wants the result.
-// Rank 0 also writes that part's header.  If the whole does not fit `dst_bytes` nothing but the
-// header is written; the reader refuses it by its size.
-__global__ void __launch_bounds__(256) result_header_kernel(const Counters *ctr, unsigned long long *h) {
+// A rank's four header words alone (for a slot too small to take the part: the reader then sees
+// part_bytes > slot and refuses it).
+__global__ void result_header_kernel(const Counters *ctr, unsigned long long *h) {
     const unsigned long long n = ctr->n_out, blob = ctr->blob_bytes;
     h[0] = n; h[1] = blob; h[2] = ctr->total; h[3] = (32ull + 8ull * (n + 1) + 16ull * n + blob + 31ull) & ~31ull;
-}
-__global__ void __launch_bounds__(256) result_push_kernel(ReduceBufs red, const unsigned long long *__restrict__ headers,
-                                                          uint32_t rank, uint32_t world, uint8_t *dst, uint64_t dst_bytes) {
-    unsigned long long n_tot = 0, blob_tot = 0, total_tot = 0, n_base = 0, blob_base = 0, total_base = 0;
-    for (uint32_t r = 0; r < world; ++r) {
-        if (r == rank) { n_base = n_tot; blob_base = blob_tot; total_base = total_tot; }
-        n_tot += headers[4 * r]; blob_tot += headers[4 * r + 1]; total_tot += headers[4 * r + 2];
-    }
-    const unsigned long long n = headers[4 * rank], blob = headers[4 * rank + 1];
-    const unsigned long long bytes = (32ull + 8ull * (n_tot + 1) + 16ull * n_tot + blob_tot + 31ull) & ~31ull;
-    unsigned long long *h = reinterpret_cast<unsigned long long *>(dst);
-    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x, tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (rank == 0 && tid == 0) { h[0] = n_tot; h[1] = blob_tot; h[2] = total_tot; h[3] = bytes; }
-    if (bytes <= dst_bytes) {
-        unsigned long long *off = h + 4, *cnt = off + n_tot + 1, *val = cnt + n_tot;
-        uint8_t *kb = reinterpret_cast<uint8_t *>(val + n_tot);
-        // offsets [n_base, n_base + n) belong to this rank; the closing offset to the last rank
-        for (uint64_t i = tid; i < n; i += stride) {
-            off[n_base + i] = red.key_offsets[i] + blob_base;
-            cnt[n_base + i] = red.counts[i];
-            val[n_base + i] = red.vals[i] + total_base;
-        }
-        if (rank == world - 1 && tid == 0) off[n_tot] = blob_tot;
-        for (uint64_t i = tid; i < blob; i += stride) kb[blob_base + i] = red.key_blob[i];
-    }
     __threadfence_system();
 }
-
 int launch_result_header(const Counters *ctr, unsigned long long *dev_hdr, cudaStream_t st) {
     result_header_kernel<<<1, 1, 0, st>>>(ctr, dev_hdr);
-    return 1;
-}
-int launch_result_push(ReduceBufs red, const unsigned long long *headers, uint32_t rank, uint32_t world, uint8_t *dst,
-                       uint64_t dst_bytes, uint64_t n_hint, int num_sms, cudaStream_t st) {
-    result_push_kernel<<<grid_for(n_hint * 16 + 1024, num_sms), 256, 0, st>>>(red, headers, rank, world, dst, dst_bytes);
     return 1;
 }
 

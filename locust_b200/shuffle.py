@@ -109,34 +109,40 @@ class PeerExchange:
     slot holds `short_cap` short records plus `long_room` bytes of long records; short_cap is the
     sender's table size, so short records can never overflow."""
 
-    def __init__(self, wc, dist, device, table_slots, long_room=16 << 20, group=None):
+    def __init__(self, wc, dist, device, table_slots, long_room=16 << 20, group=None, result_room=None):
         import torch
         self.wc, self.dist, self.group = wc, dist, group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self.short_cap = int(table_slots)
         self.slot_bytes = 32 + 32 * self.short_cap + int(long_room)
         self.slot_bytes = (self.slot_bytes + 31) // 32 * 32
-        # only rank 0 receives the gather; everyone receives the hash shuffle.  A rank that cannot
-        # allocate still takes part in the all-gather (with an empty handle) so nobody hangs.
-        self.mine, self.bufs, raw = [], [], bytes(128)
+        # ordered jobs: rank 0 owns one slot per rank for that rank's sorted slice (offsets, counts, vals
+        # and key bytes of as many keys as a table has slots, 24 key bytes each on average)
+        self.result_slot = (int(result_room) if result_room else 64 + 48 * self.short_cap + 31) // 32 * 32
+        # only rank 0 receives the gather and the result; everyone receives the shuffle.  A rank that
+        # cannot allocate still takes part in the all-gather (with an empty handle) so nobody hangs.
+        nbuf = 3
+        self.mine, self.bufs, raw = [], [], bytes(64 * nbuf)
         try:
             self.mine = [wc.exchange_alloc(self.slot_bytes * self.world),
-                         wc.exchange_alloc(self.slot_bytes * (self.world if self.rank == 0 else 1))]
-            raw = wc.ipc_export(self.mine[0]) + wc.ipc_export(self.mine[1])
+                         wc.exchange_alloc(self.slot_bytes * (self.world if self.rank == 0 else 1)),
+                         wc.exchange_alloc(self.result_slot * self.world if self.rank == 0 else 64)]
+            raw = b"".join(wc.ipc_export(m) for m in self.mine)
         except Exception:                                        # noqa: BLE001 - raised below, on every rank
             pass
         handles = torch.tensor(list(raw), dtype=torch.uint8, device=device)
-        allh = torch.empty(self.world * 128, dtype=torch.uint8, device=device)
+        allh = torch.empty(self.world * 64 * nbuf, dtype=torch.uint8, device=device)
         dist.all_gather_into_tensor(allh, handles, group=group)
         allh = bytes(allh.cpu().numpy())
-        if any(allh[r * 128:(r + 1) * 128] == bytes(128) for r in range(self.world)):
+        per = 64 * nbuf
+        if any(allh[r * per:(r + 1) * per] == bytes(per) for r in range(self.world)):
             raise RuntimeError("a rank could not allocate or export its exchange buffers")
-        for r in range(self.world):          # bufs[r] = (shuffle buffer, gather buffer) of rank r, as seen from here
+        for r in range(self.world):     # bufs[r] = (shuffle, gather, result buffer) of rank r, as seen from here
             if r == self.rank:
-                self.bufs.append((self.mine[0], self.mine[1]))
+                self.bufs.append(tuple(self.mine))
             else:
-                h = allh[r * 128:(r + 1) * 128]
-                self.bufs.append((wc.ipc_open(h[:64]), wc.ipc_open(h[64:])))
+                h = allh[r * per:(r + 1) * per]
+                self.bufs.append(tuple(wc.ipc_open(h[64 * i:64 * (i + 1)]) for i in range(nbuf)))
         self._token = torch.zeros(1, dtype=torch.int32, device=device)
 
     def barrier(self):
@@ -145,10 +151,10 @@ class PeerExchange:
         self.dist.all_reduce(self._token, group=self.group)
 
     def close(self):
-        for r, (a, b) in enumerate(self.bufs):
+        for r, mapped in enumerate(self.bufs):
             if r != self.rank:
-                self.wc.ipc_close(a)
-                self.wc.ipc_close(b)
+                for m in mapped:
+                    self.wc.ipc_close(m)
         self.bufs = []
 
 
@@ -207,6 +213,22 @@ class DistributedWordCount:
         for s in range(nslots):
             wc.shuffle_merge(px.mine[which] + s * px.slot_bytes, px.slot_bytes)
 
+    def _push_results(self):
+        """the same over peer memory: every rank packs its slice straight into its slot of rank 0's
+        result buffer; barrier; rank 0 strings the slots together"""
+        wc, px = self.b.wc, self.peers
+        nbytes = wc.result_part_bytes()
+        dst = px.bufs[0][2] + self.rank * px.result_slot
+        if nbytes <= px.result_slot:
+            wc.result_part_pack(dst)
+        else:
+            wc.result_header(dst)                 # rank 0 sees the size and refuses the job as well
+        px.barrier()
+        if self.rank == 0:
+            wc.result_adopt_slots(px.mine[2], px.result_slot, self.world)
+        if nbytes > px.result_slot:
+            raise RuntimeError("sorted slice of %d bytes does not fit its %d-byte slot on rank 0" % (nbytes, px.result_slot))
+
     def _gather_results(self):
         """every rank's sorted slice goes to rank 0, which strings them together in rank order"""
         b = self.b
@@ -240,7 +262,10 @@ class DistributedWordCount:
                 self.last_shuffle_bytes = sum(s for r, s in enumerate(sent) if r != self.rank)
             b.process()
             b.reduce()
-            self._gather_results()
+            if self.peers is not None:
+                self._push_results()
+            else:
+                self._gather_results()
             return self
         if self.world > 1 and self.peers is not None:
             self._shuffle_peers(0, list(range(self.world)))

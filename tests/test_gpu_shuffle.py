@@ -195,7 +195,7 @@ def test_pack_straight_into_peer_slots(lb, P):
             c.close()
 
 
-def emulate_ordered(lb, data, P, **kw):
+def emulate_ordered(lb, data, P, via="concat", room=None, **kw):
     """the ordered shuffle over P emulated ranks: parts are key ranges, every rank sorts its own
     range, rank 0 strings the slices together.  Returns rank 0's (keys, counts, vals) and the
     per-rank slices [(keys, counts)]."""
@@ -239,6 +239,20 @@ def emulate_ordered(lb, data, P, **kw):
         torch.cuda.synchronize()
         headers = [p[:32].view(torch.int64).tolist() for p in parts]
         assert all(h[3] == p.numel() for h, p in zip(headers, parts))
+        if via == "slots":
+            # what ranks on one box do: every slice packed into its slot of one buffer, strung together from there
+            slot = room if room is not None else (max(p.numel() for p in parts) + 64) // 32 * 32
+            landing = torch.zeros(slot * P, dtype=torch.uint8, device="cuda")
+            torch.cuda.synchronize()
+            for r in range(P):
+                if parts[r].numel() <= slot:
+                    ctx[r].result_part_pack(landing.data_ptr() + r * slot)
+                else:
+                    ctx[r].result_header(landing.data_ptr() + r * slot)
+            torch.cuda.synchronize()
+            ctx[0].result_adopt_slots(landing.data_ptr(), slot, P)
+            keys, counts, vals = ctx[0].result()
+            return keys, counts, vals, slices, ctx[0].stats()
         ctx[0].result_concat([p.data_ptr() for p in parts], [h[0] for h in headers], [h[1] for h in headers],
                              [h[2] for h in headers], keepalive=parts)
         keys, counts, vals = ctx[0].result()
@@ -262,6 +276,22 @@ def test_ordered_shuffle_matches_the_oracle(lb, P):
     assert flat == ref.keys
     if P > 1:
         assert max(len(ks) for ks, _ in slices) < len(ref.keys)
+
+
+@pytest.mark.parametrize("P", [1, 2, 8])
+def test_ordered_shuffle_slices_in_slots(lb, P):
+    from oracle import pyoracle
+    data = golden_input("hamlet") + golden_input("edge_long_tokens") + b" " + golden_input("rand_longtok_s5")
+    keys, counts, vals, _, stats = emulate_ordered(lb, data, P, via="slots", table_log2=14)
+    ref = pyoracle.wordcount(data)
+    assert keys == ref.keys and counts == ref.counts
+    assert vals == [sum(ref.counts[:i]) for i in range(len(ref.counts))]
+    assert stats["unique_keys"] == len(ref.keys) and stats["tokens"] == sum(ref.counts)
+    # slots that are too small are refused, not half filled
+    with pytest.raises(lb.LocustError):
+        emulate_ordered(lb, data, P, via="slots", room=4096, table_log2=14)
+    keys, counts, _, _, _ = emulate_ordered(lb, b"", P, via="slots", table_log2=10)
+    assert keys == [] and counts == []
 
 
 def test_ordered_shuffle_every_first_byte_and_tiny_inputs(lb):
