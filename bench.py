@@ -222,7 +222,7 @@ def main():
             ok = torch.ones(1, dtype=torch.int32, device=dev)
             with torch.cuda.stream(stream):
                 try:
-                    peers = PeerExchange(wc, dist, dev, 1 << table_log2)
+                    peers = PeerExchange(wc, dist, dev, 1 << table_log2, ordered=args.final == "ordered")
                 except Exception as e:                       # noqa: BLE001 - reported, then agreed on below
                     sys.stderr.write("rank %d: peer exchange unavailable (%s)\n" % (rank, e))
                     ok.zero_()

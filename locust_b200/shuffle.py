@@ -109,7 +109,7 @@ class PeerExchange:
     slot holds `short_cap` short records plus `long_room` bytes of long records; short_cap is the
     sender's table size, so short records can never overflow."""
 
-    def __init__(self, wc, dist, device, table_slots, long_room=16 << 20, group=None, result_room=None):
+    def __init__(self, wc, dist, device, table_slots, long_room=16 << 20, group=None, result_room=None, ordered=None):
         import torch
         self.wc, self.dist, self.group = wc, dist, group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
@@ -124,9 +124,12 @@ class PeerExchange:
         nbuf = 3
         self.mine, self.bufs, raw = [], [], bytes(64 * nbuf)
         try:
+            # ordered=True / False: only the buffers that kind of job uses (None: both)
+            need_gather = self.rank == 0 and ordered is not True
+            need_result = self.rank == 0 and ordered is not False
             self.mine = [wc.exchange_alloc(self.slot_bytes * self.world),
-                         wc.exchange_alloc(self.slot_bytes * (self.world if self.rank == 0 else 1)),
-                         wc.exchange_alloc(self.result_slot * self.world if self.rank == 0 else 64)]
+                         wc.exchange_alloc(self.slot_bytes * self.world if need_gather else 64),
+                         wc.exchange_alloc(self.result_slot * self.world if need_result else 64)]
             raw = b"".join(wc.ipc_export(m) for m in self.mine)
         except Exception:                                        # noqa: BLE001 - raised below, on every rank
             pass

@@ -17,6 +17,7 @@ from locust_b200.shuffle import DistributedWordCount, GpuBackend, PeerExchange
 ap = argparse.ArgumentParser()
 ap.add_argument("--configs", default="C3,C5,C4")
 ap.add_argument("--gib", type=float, default=0.0, help="override the total size (GiB)")
+ap.add_argument("--final", default="ordered", choices=["ordered", "gather"])
 a = ap.parse_args()
 rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(lr); dev = torch.device("cuda", lr)
@@ -44,8 +45,9 @@ for name in a.configs.split(","):
         wc.run(text)
         local_tokens = wc.stats()["tokens"]
         lb, lo, lc, _ = wc.result_arrays()
-        peers = PeerExchange(wc, dist, dev, 1 << log2) if name != "C4" else None     # C4: slots of 4 GB each, use NCCL
-        job = DistributedWordCount(GpuBackend(wc, dev), dist, peers=peers)
+        ordered = a.final == "ordered"
+        peers = PeerExchange(wc, dist, dev, 1 << log2, ordered=ordered) if name != "C4" else None     # C4: slots of 4 GB each, use NCCL
+        job = DistributedWordCount(GpuBackend(wc, dev), dist, peers=peers, ordered=ordered)
         job.run(text)                                                                 # warm-up
         dist.barrier(); torch.cuda.synchronize(); t0 = time.perf_counter()
         job.run(text)
@@ -82,7 +84,7 @@ for name in a.configs.split(","):
         print(json.dumps({"config": name, "n_gpus": world, "bytes": per * world, "tokens": int(tok.item()),
                           "unique_keys": int(len(counts)), "seconds": dt, "gbs": per * world / dt / 1e9,
                           "sorted_unique": sorted_unique, "sum_counts_equals_tokens": sums_ok, "vals_are_prefix_sums": vals_ok,
-                          "sampled_counts_add_up_over_ranks": sample_ok, "exchange": "peers" if peers else "nccl"}), flush=True)
+                          "sampled_counts_add_up_over_ranks": sample_ok, "exchange": "peers" if peers else "nccl", "final_stage": a.final}), flush=True)
     if peers:
         peers.close()
     wc.close(); del text
