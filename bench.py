@@ -346,6 +346,21 @@ def main():
            "d2h_bytes_per_step": d2h, "steps": e2e_steps,
            "note": "locust_map(LOCUST_HOST) from pinned memory, chunked copy overlapped with map; result copied to host"}
 
+    if world == 1:
+        # what the link delivers for the same bytes: a bare pinned host -> device copy, no word count
+        scratch = torch.empty(per_gpu, dtype=torch.uint8, device=dev)
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            scratch.copy_(host, non_blocking=True)
+            c0.record(stream)
+            for _ in range(3):
+                scratch.copy_(host, non_blocking=True)
+            c1.record(stream)
+        torch.cuda.synchronize()
+        e2e["bare_h2d_copy_gbs"] = 3 * per_gpu / (c0.elapsed_time(c1) * 1e-3) / GB
+        e2e["frac_of_bare_copy"] = e2e["value"] / e2e["bare_h2d_copy_gbs"]
+        del scratch
+
     clocks = sampler.stop(m0, m1)
 
     # ---- the reference's CPU algorithm on this box's host cores (rank 0, N=1) -----------------
