@@ -255,21 +255,25 @@ __global__ void __launch_bounds__(256) sort_all_kernel(Records r, const uint32_t
         active |= (ctr->pass_active[pass] ? 1u : 0u) << pass;
         from_b |= (ctr->pass_src[pass] ? 1u : 0u) << pass;
     }
+    // few tiles (one round): dealt by block index, no ticket traffic -- and blocks without a tile leave
+    // at once, so the barrier is between the working blocks only; many tiles: tickets balance the load
+    const bool by_index = n <= (unsigned long long)gridDim.x * kSortTile;
+    const uint32_t members = by_index ? (uint32_t)((n + kSortTile - 1) / kSortTile) : gridDim.x;
+    if (by_index && blockIdx.x >= members) return;
     for (int pass = 0; pass < 16; ++pass) {
         if (!((active >> pass) & 1u)) continue;                     // the same decision in every block
-        // few tiles (one round): dealt by block index, no ticket traffic; many tiles: tickets balance the load
-        sort_one_pass(n <= (unsigned long long)gridDim.x * kSortTile, r, bases, n, ((from_b >> pass) & 1u) != 0u, pass,
+        sort_one_pass(by_index, r, bases, n, ((from_b >> pass) & 1u) != 0u, pass,
                       lb_state, tickets + 2 * pass, epoch + (uint32_t)pass);
         ++generation;
         __syncthreads();
         if (threadIdx.x == 0) {
             __threadfence();
             atomicAdd(bar, 1u);
-            const uint32_t want = generation * gridDim.x;
+            const uint32_t want = generation * members;
             uint32_t seen;
             do {
                 asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(bar) : "memory");
-                if (seen < want) __nanosleep(32);
+                if (seen < want && members > 64u) __nanosleep(32);
             } while (seen < want);
             __threadfence();
         }
