@@ -86,8 +86,8 @@ class ClockSampler(threading.Thread):
 def workload(n_gpus):
     if n_gpus == 1:
         return "C2", 1 << 30, "C2: 1 GiB synthetic Zipf(s=1.1) English-like text, 50K vocab, word count on 1xB200"
-    return "C3", 2 << 30, ("C3 text (Zipf s=1.1, 1M vocab), 2 GiB per GPU cut on delimiters (N=8 is the 16 GiB config), "
-                           "hash-partitioned NCCL all-to-all shuffle")
+    return "C3", (16 << 30) // n_gpus, ("C3: 16 GiB synthetic Zipf(s=1.1) text, 1M-word vocab, sharded by byte range cut on "
+                                        "delimiters across %d B200 (%d GiB per GPU), shuffle over NVLink" % (n_gpus, 16 // n_gpus))
 
 
 def cpu_port_rate(sample, threads=1):
@@ -148,7 +148,7 @@ def run_reference(args, rank, world):
     value = sample_bytes * len(times) / tot / GB
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": desc},
             "cpu_baseline": {"value": value, "unit": "GB/s", "cores": 1, "kind": "port",
                              "sample": "first %d MiB of the workload text; map -> comparison sort of every token "
@@ -379,11 +379,13 @@ def main():
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic",
                 "config": {"workload": desc, "bytes_per_gpu": per_gpu, "tokens_per_gpu": tokens if world == 1 else None,
                            "unique_keys": uniq, "table_log2": table_log2, "input_sha256": input_id,
                            "final_stage": (args.final if world > 1 else None),
+                           "series": "N=1 is BASELINE config 2 (1 GiB, 50K vocab); N=2/4/8 are config 3 (16 GiB in total, "
+                                     "1M vocab): total work is fixed from N=2 on",
                            "l2": "input per step (%d MiB per GPU) is larger than the 126 MB L2" % (per_gpu >> 20)},
                 "roofline": roofline, "shuffle": shuffle, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
                 "gpu_launches": launches_per_step * args.steps, "gpu_launches_per_step": launches_per_step,
