@@ -228,6 +228,20 @@ int locust_result_concat(locust_ctx *ctx, uint32_t nparts, const void *const *de
 int locust_result_header(locust_ctx *ctx, void *dev_header);
 int locust_result_adopt_slots(locust_ctx *ctx, const void *dev_slots, uint64_t slot_bytes, uint32_t nslots);
 
+/* Small helpers over the same peer mappings, so that a job on one box needs no collective call:
+ * locust_peer_put copies nbytes (multiple of 16) from dev_src to each of the ndst destinations
+ *   (a rank's histogram into its slot on every rank);
+ * locust_partition_by_range_sum is locust_partition_by_range over nhists histograms that lie
+ *   one after the other, added up on the fly (the slots the ranks put theirs into);
+ * locust_peer_barrier orders the ranks' streams: peer_flags[p] is rank p's array of `world`
+ *   uint32 flags (zero before first use, mapped by every rank); work queued after it on this
+ *   stream starts only when every rank's stream has reached its barrier with the same epoch
+ *   (1, 2, 3, ... per use).  It waits on the GPU, not on the host; after five seconds without
+ *   a peer it gives up and the job fails at locust_reduce / locust_result_adopt_slots. */
+int locust_peer_put(locust_ctx *ctx, uint32_t ndst, void *const *dsts, const void *dev_src, uint64_t nbytes);
+int locust_partition_by_range_sum(locust_ctx *ctx, const void *dev_hists, uint32_t nhists, uint32_t nparts);
+int locust_peer_barrier(locust_ctx *ctx, void *const *peer_flags, uint32_t rank, uint32_t world, uint32_t epoch);
+
 /* ---- for callers that cannot allocate ------------------------------------------
  * No counterpart in the reference (its main() allocates freely, main.cu:393,:402,:451).
  *

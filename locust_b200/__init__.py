@@ -28,7 +28,8 @@ EXPORTS = [
     "locust_map_intermediate", "locust_exchange_alloc", "locust_ipc_export", "locust_ipc_open", "locust_ipc_close",
     "locust_shuffle_pack_peers", "locust_partition_histogram", "locust_partition_by_range",
     "locust_result_part_bytes", "locust_result_part_pack", "locust_result_concat",
-    "locust_result_header", "locust_result_adopt_slots",
+    "locust_result_header", "locust_result_adopt_slots", "locust_peer_put", "locust_partition_by_range_sum",
+    "locust_peer_barrier",
 ]
 PARTITION_BINS = 65536
 STATIC_MAX_KEYS = 16384
@@ -96,6 +97,9 @@ def load():
     L.locust_result_concat.argtypes = [vp, u32, pp(vp), pp(u64), pp(u64), pp(u64)]
     L.locust_result_header.argtypes = [vp, vp]
     L.locust_result_adopt_slots.argtypes = [vp, vp, u64, u32]
+    L.locust_peer_put.argtypes = [vp, u32, pp(vp), vp, u64]
+    L.locust_partition_by_range_sum.argtypes = [vp, vp, u32, u32]
+    L.locust_peer_barrier.argtypes = [vp, pp(vp), u32, u32, u32]
     _lib = L
     return L
 
@@ -319,6 +323,18 @@ class WordCount:
 
     def result_header(self, dev_header_ptr):
         self._check(self._L.locust_result_header(self._h, dev_header_ptr), "locust_result_header")
+
+    def peer_put(self, dsts, dev_src_ptr, nbytes):
+        arr = (ctypes.c_void_p * len(dsts))(*dsts)
+        self._check(self._L.locust_peer_put(self._h, len(dsts), arr, dev_src_ptr, nbytes), "locust_peer_put")
+
+    def partition_by_range_sum(self, dev_hists_ptr, nhists, nparts):
+        self._check(self._L.locust_partition_by_range_sum(self._h, dev_hists_ptr, nhists, nparts),
+                    "locust_partition_by_range_sum")
+
+    def peer_barrier(self, flag_ptrs, rank, world, epoch):
+        arr = (ctypes.c_void_p * len(flag_ptrs))(*flag_ptrs)
+        self._check(self._L.locust_peer_barrier(self._h, arr, rank, world, epoch), "locust_peer_barrier")
 
     def result_adopt_slots(self, dev_slots_ptr, slot_bytes, nslots):
         self._check(self._L.locust_result_adopt_slots(self._h, dev_slots_ptr, slot_bytes, nslots),

@@ -137,7 +137,12 @@ int launch_shuffle_pack_peers(const Slot *table, uint64_t slots, const LongOcc *
 // ordered shuffle: histogram of the keys' first two bytes (65 536 bins), bin -> part map
 int launch_partition_hist(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
                           const Counters *ctr, unsigned long long *hist, int num_sms, cudaStream_t st);
-int launch_partition_map(const unsigned long long *hist, uint32_t nparts, uint8_t *partmap, cudaStream_t st);
+int launch_partition_map(const unsigned long long *hist, uint32_t nhists, unsigned long long *sum_scratch,
+                         uint32_t nparts, uint8_t *partmap, cudaStream_t st);
+// peer memory: the same words to several destinations; a barrier between the ranks' streams
+int launch_peer_put(uint4 *const *dev_dsts, uint32_t ndst, const uint4 *src, uint64_t n16, int num_sms, cudaStream_t st);
+int launch_peer_barrier(uint32_t *const *dev_flags, uint32_t rank, uint32_t world, uint32_t epoch, uint32_t *xflag,
+                        cudaStream_t st);
 // a sorted result as one part {header, offsets, counts, vals, key bytes}; appending parts to a result
 int launch_result_pack(ReduceBufs red, const Counters *ctr, uint8_t *out, uint64_t n_hint, int num_sms, cudaStream_t st);
 int launch_result_header(const Counters *ctr, unsigned long long *dev_hdr, cudaStream_t st);

@@ -70,6 +70,9 @@ struct locust_ctx {
     unsigned long long *part_dev = nullptr;  uint32_t part_cap = 0;
     std::vector<unsigned long long> part_host, part_off_host;
     uint32_t part_n = 0;
+    unsigned long long *peer_ptrs = nullptr;  // device copies of pointer lists: [0,256) put destinations, [256,512) barrier flags
+    std::vector<unsigned long long> peer_put_host, peer_flag_host;
+    unsigned long long *hist_sum = nullptr;  // ordered shuffle: the ranks' histograms added up
     uint8_t *partmap = nullptr;              // ordered shuffle: first two key bytes -> part (65 536 entries)
     uint32_t partmap_n = 0;                  // parts the map was built for; 0 = shuffle by hash
     // direct exchange: overflow flag of pack_peers (device + pinned mirror), receive buffers we own
@@ -301,6 +304,8 @@ int finish_reduce(locust_ctx *c) {
         int rc = run_reduce_async(c);
         if (rc) return rc;
         CU(cudaStreamSynchronize(c->stream));
+        if (*c->h_xflag & 4u)
+            return fail(c, LOCUST_E_STATE, "locust_peer_barrier: a rank did not arrive within five seconds");
         if (*c->h_xflag & 2u)
             return fail(c, LOCUST_E_CAPACITY, "MAP overflowed the combiner table or the long-token list before "
                                               "locust_shuffle_pack_peers (raise table_log2 / long_capacity)");
@@ -414,7 +419,7 @@ int locust_destroy(locust_ctx *c) {
     cudaFree(c->table); cudaFree(c->long_list); cudaFree(c->ctr);
     free_record_buffers(c);
     cudaFree(c->sort.hist); cudaFree(c->sort.bases); cudaFree(c->sort.tickets);
-    cudaFree(c->line_off); cudaFree(c->d_text); cudaFree(c->part_dev); cudaFree(c->xflag); cudaFree(c->partmap);
+    cudaFree(c->line_off); cudaFree(c->d_text); cudaFree(c->part_dev); cudaFree(c->xflag); cudaFree(c->partmap); cudaFree(c->peer_ptrs); cudaFree(c->hist_sum);
     for (void *b : c->exchange_bufs) cudaFree(b);
     cudaFreeHost(c->h_xflag);
     cudaFreeHost(c->h_ctr); cudaFreeHost(c->h_blob); cudaFreeHost(c->h_offsets);
@@ -806,16 +811,61 @@ int locust_partition_histogram(locust_ctx *c, void *dev_hist) {
 }
 
 int locust_partition_by_range(locust_ctx *c, const void *dev_hist, uint32_t nparts) {
+    return locust_partition_by_range_sum(c, dev_hist, 1, nparts);
+}
+
+int locust_partition_by_range_sum(locust_ctx *c, const void *dev_hist, uint32_t nhists, uint32_t nparts) {
     if (!c) return LOCUST_E_ARG;
     if (c->stage != 0) return fail(c, LOCUST_E_STATE, "locust_partition_by_range after locust_process");
     if (nparts == 0) { c->partmap_n = 0; return LOCUST_OK; }       // back to the hash shuffle
     if (!dev_hist) return LOCUST_E_ARG;
-    if (nparts > 256) return fail(c, LOCUST_E_ARG, "locust_partition_by_range: at most 256 parts");
+    if (nparts > 256 || nhists == 0 || nhists > 256)
+        return fail(c, LOCUST_E_ARG, "locust_partition_by_range: at most 256 parts, 1 to 256 histograms");
     CU(cudaSetDevice(c->device));
     if (!c->partmap) CU(dalloc(&c->partmap, (uint64_t)LOCUST_PARTITION_BINS));
-    c->launches += (uint64_t)launch_partition_map(static_cast<const unsigned long long *>(dev_hist), nparts, c->partmap, c->stream);
+    if (nhists > 1 && !c->hist_sum) CU(dalloc(&c->hist_sum, (uint64_t)LOCUST_PARTITION_BINS));
+    c->launches += (uint64_t)launch_partition_map(static_cast<const unsigned long long *>(dev_hist), nhists, c->hist_sum, nparts, c->partmap, c->stream);
     CU(cudaGetLastError());
     c->partmap_n = nparts;
+    return LOCUST_OK;
+}
+
+// device copy of a short pointer list, refreshed only when the list changes
+static int stage_pointers(locust_ctx *c, std::vector<unsigned long long> &cache, uint32_t at, uint32_t n, void *const *ptrs) {
+    if (!c->peer_ptrs) CU(dalloc(&c->peer_ptrs, 512));
+    bool same = cache.size() == n;
+    for (uint32_t i = 0; same && i < n; ++i) same = cache[i] == reinterpret_cast<unsigned long long>(ptrs[i]);
+    if (same) return LOCUST_OK;
+    CU(cudaStreamSynchronize(c->stream));            // an earlier kernel may still be reading the old list
+    cache.resize(n);
+    for (uint32_t i = 0; i < n; ++i) cache[i] = reinterpret_cast<unsigned long long>(ptrs[i]);
+    CU(cudaMemcpyAsync(c->peer_ptrs + at, cache.data(), n * sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
+    return LOCUST_OK;
+}
+
+int locust_peer_put(locust_ctx *c, uint32_t ndst, void *const *dsts, const void *dev_src, uint64_t nbytes) {
+    if (!c || !dsts || !dev_src || ndst == 0 || ndst > 256) return LOCUST_E_ARG;
+    if (nbytes % 16 || reinterpret_cast<uintptr_t>(dev_src) % 16) return fail(c, LOCUST_E_ARG, "locust_peer_put: 16-byte units");
+    for (uint32_t i = 0; i < ndst; ++i)
+        if (!dsts[i] || reinterpret_cast<uintptr_t>(dsts[i]) % 16) return fail(c, LOCUST_E_ARG, "locust_peer_put: destinations must be 16-byte aligned");
+    CU(cudaSetDevice(c->device));
+    int rc = stage_pointers(c, c->peer_put_host, 0, ndst, dsts);
+    if (rc) return rc;
+    c->launches += (uint64_t)launch_peer_put(reinterpret_cast<uint4 *const *>(c->peer_ptrs), ndst, static_cast<const uint4 *>(dev_src),
+                                             nbytes / 16, c->num_sms, c->stream);
+    CU(cudaGetLastError());
+    return LOCUST_OK;
+}
+
+int locust_peer_barrier(locust_ctx *c, void *const *peer_flags, uint32_t rank, uint32_t world, uint32_t epoch) {
+    if (!c || !peer_flags || world == 0 || world > 256 || rank >= world) return LOCUST_E_ARG;
+    for (uint32_t i = 0; i < world; ++i)
+        if (!peer_flags[i] || reinterpret_cast<uintptr_t>(peer_flags[i]) % 4) return fail(c, LOCUST_E_ARG, "locust_peer_barrier: NULL or unaligned flag array");
+    CU(cudaSetDevice(c->device));
+    int rc = stage_pointers(c, c->peer_flag_host, 256, world, peer_flags);
+    if (rc) return rc;
+    c->launches += (uint64_t)launch_peer_barrier(reinterpret_cast<uint32_t *const *>(c->peer_ptrs + 256), rank, world, epoch, c->xflag, c->stream);
+    CU(cudaGetLastError());
     return LOCUST_OK;
 }
 
@@ -895,7 +945,9 @@ int locust_result_adopt_slots(locust_ctx *c, const void *dev_slots, uint64_t slo
     CU(cudaSetDevice(c->device));
     uint64_t h[256 * 4];
     CU(cudaMemcpy2DAsync(h, 32, dev_slots, slot_bytes, 32, nslots, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(c->h_xflag, c->xflag, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
+    if (*c->h_xflag & 4u) return fail(c, LOCUST_E_STATE, "locust_peer_barrier: a rank did not arrive within five seconds");
     const void *parts[256];
     uint64_t n[256], blob[256], total[256];
     for (uint32_t i = 0; i < nslots; ++i) {

@@ -241,8 +241,16 @@ __global__ void __launch_bounds__(256) partition_hist_kernel(const Slot *__restr
 // a contiguous key range below part p + 1's, and the ranges hold about total / nparts keys each
 // (as far as whole bins allow).  Every rank computes the same map from the same all-reduced
 // histogram.
-__global__ void __launch_bounds__(1024) partition_map_kernel(const unsigned long long *__restrict__ hist, uint32_t nparts,
-                                                             uint8_t *partmap) {
+// nhists histograms that lie one after the other (one per rank, put there over peer memory) added up
+__global__ void __launch_bounds__(256) hist_sum_kernel(const unsigned long long *__restrict__ hists, uint32_t nhists,
+                                                       unsigned long long *__restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;      // 65 536 threads
+    unsigned long long v = 0;
+    for (uint32_t h = 0; h < nhists; ++h) v += hists[(uint64_t)h * 65536u + i];
+    out[i] = v;
+}
+__global__ void __launch_bounds__(1024) partition_map_kernel(const unsigned long long *__restrict__ hist,
+                                                             uint32_t nparts, uint8_t *partmap) {
     __shared__ unsigned long long warp_sum[32];
     const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
     const unsigned long long *mine = hist + w * 2048u;
@@ -281,8 +289,56 @@ int launch_partition_hist(const Slot *table, uint64_t slots, const LongOcc *long
     partition_hist_kernel<<<grid_for(slots, num_sms), 256, 0, st>>>(table, slots, long_list, long_cap, ctr, hist);
     return 1;
 }
-int launch_partition_map(const unsigned long long *hist, uint32_t nparts, uint8_t *partmap, cudaStream_t st) {
+int launch_partition_map(const unsigned long long *hist, uint32_t nhists, unsigned long long *sum_scratch,
+                         uint32_t nparts, uint8_t *partmap, cudaStream_t st) {
+    if (nhists > 1) {
+        hist_sum_kernel<<<256, 256, 0, st>>>(hist, nhists, sum_scratch);
+        hist = sum_scratch;
+    }
     partition_map_kernel<<<1, 1024, 0, st>>>(hist, nparts, partmap);
+    return nhists > 1 ? 2 : 1;
+}
+
+// ---- small transfers and a barrier over peer memory (one box, buffers mapped with locust_ipc_*) ------
+// The same 16-byte words to every destination (a rank's histogram to all ranks, say).
+__global__ void __launch_bounds__(256) peer_put_kernel(uint4 *const *__restrict__ dsts, uint32_t ndst,
+                                                       const uint4 *__restrict__ src, uint64_t n16) {
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) {
+        const uint4 v = src[i];
+        for (uint32_t d = 0; d < ndst; ++d) dsts[d][i] = v;
+    }
+    __threadfence_system();
+}
+// Barrier between the ranks' streams: thread p tells rank p "rank `rank` has reached `epoch`"
+// (flags[p][rank] = epoch, a store into p's memory) and then waits until rank p has told us the
+// same (flags[rank][p] >= epoch, a load from our own memory).  Everything this stream wrote to
+// peers before is visible to them once they pass.  Gives up after five seconds (a rank that
+// died must not hang the others' GPUs) and says so in *xflag.
+__global__ void peer_barrier_kernel(uint32_t *const *__restrict__ flags, uint32_t rank, uint32_t world, uint32_t epoch,
+                                    uint32_t *xflag) {
+    const uint32_t p = threadIdx.x;
+    if (p >= world) return;
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flags[p] + rank), "r"(epoch) : "memory");
+    const uint32_t *mine = flags[rank] + p;
+    unsigned long long t0, t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+    for (;;) {
+        uint32_t seen;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(mine) : "memory");
+        if ((int32_t)(seen - epoch) >= 0) break;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+        if (t - t0 > 5000000000ull) { atomicOr(xflag, 4u); break; }
+    }
+}
+int launch_peer_put(uint4 *const *dev_dsts, uint32_t ndst, const uint4 *src, uint64_t n16, int num_sms, cudaStream_t st) {
+    peer_put_kernel<<<grid_for(n16, num_sms), 256, 0, st>>>(dev_dsts, ndst, src, n16);
+    return 1;
+}
+int launch_peer_barrier(uint32_t *const *dev_flags, uint32_t rank, uint32_t world, uint32_t epoch, uint32_t *xflag,
+                        cudaStream_t st) {
+    peer_barrier_kernel<<<1, 256, 0, st>>>(dev_flags, rank, world, epoch, xflag);
     return 1;
 }
 

@@ -109,7 +109,10 @@ class PeerExchange:
     slot holds `short_cap` short records plus `long_room` bytes of long records; short_cap is the
     sender's table size, so short records can never overflow."""
 
-    def __init__(self, wc, dist, device, table_slots, long_room=16 << 20, group=None, result_room=None, ordered=None):
+    HIST_BYTES = 65536 * 8
+
+    def __init__(self, wc, dist, device, table_slots, long_room=16 << 20, group=None, result_room=None, ordered=None,
+                 flag_barrier=True):
         import torch
         self.wc, self.dist, self.group = wc, dist, group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
@@ -121,7 +124,9 @@ class PeerExchange:
         self.result_slot = (int(result_room) if result_room else 64 + 48 * self.short_cap + 31) // 32 * 32
         # only rank 0 receives the gather and the result; everyone receives the shuffle.  A rank that
         # cannot allocate still takes part in the all-gather (with an empty handle) so nobody hangs.
-        nbuf = 3
+        # fourth buffer: `world` barrier flags (256 bytes), then one histogram slot per rank
+        nbuf = 4
+        self.flag_barrier, self._epoch = bool(flag_barrier), 0
         self.mine, self.bufs, raw = [], [], bytes(64 * nbuf)
         try:
             # ordered=True / False: only the buffers that kind of job uses (None: both)
@@ -129,7 +134,8 @@ class PeerExchange:
             need_result = self.rank == 0 and ordered is not False
             self.mine = [wc.exchange_alloc(self.slot_bytes * self.world),
                          wc.exchange_alloc(self.slot_bytes * self.world if need_gather else 64),
-                         wc.exchange_alloc(self.result_slot * self.world if need_result else 64)]
+                         wc.exchange_alloc(self.result_slot * self.world if need_result else 64),
+                         wc.exchange_alloc(256 + self.HIST_BYTES * self.world)]
             raw = b"".join(wc.ipc_export(m) for m in self.mine)
         except Exception:                                        # noqa: BLE001 - raised below, on every rank
             pass
@@ -140,7 +146,7 @@ class PeerExchange:
         per = 64 * nbuf
         if any(allh[r * per:(r + 1) * per] == bytes(per) for r in range(self.world)):
             raise RuntimeError("a rank could not allocate or export its exchange buffers")
-        for r in range(self.world):     # bufs[r] = (shuffle, gather, result buffer) of rank r, as seen from here
+        for r in range(self.world):     # bufs[r] = (shuffle, gather, result, sync buffer) of rank r, as seen from here
             if r == self.rank:
                 self.bufs.append(tuple(self.mine))
             else:
@@ -149,9 +155,23 @@ class PeerExchange:
         self._token = torch.zeros(1, dtype=torch.int32, device=device)
 
     def barrier(self):
-        """every rank's packing kernel has finished before any rank merges: a one-element
-        all-reduce on the current stream (no host synchronisation)"""
-        self.dist.all_reduce(self._token, group=self.group)
+        """every rank's stream has got this far (its packing kernel has finished, say) before any rank's
+        stream goes on: flags written into each other's memory by a one-block kernel, or a one-element
+        all-reduce; either way on the current stream, no host synchronisation"""
+        if self.flag_barrier:
+            self._epoch += 1
+            self.wc.peer_barrier([b[3] for b in self.bufs], self.rank, self.world, self._epoch)
+        else:
+            self.dist.all_reduce(self._token, group=self.group)
+
+    def share_histogram(self, hist):
+        """puts this rank's histogram (int64[65536] on the device) into its slot on every rank; after
+        barrier() the slots of all ranks lie one after the other at hist_slots()"""
+        dsts = [b[3] + 256 + self.rank * self.HIST_BYTES for b in self.bufs]
+        self.wc.peer_put(dsts, hist.data_ptr(), self.HIST_BYTES)
+
+    def hist_slots(self):
+        return self.mine[3] + 256
 
     def close(self):
         for r, mapped in enumerate(self.bufs):
@@ -256,11 +276,15 @@ class DistributedWordCount:
         b.map(shard)
         if self.world > 1 and self.ordered:
             hist = b.histogram()
-            self.dist.all_reduce(hist, group=self.group)
-            b.partition_by_range(hist, self.world)
             if self.peers is not None:
+                # no collective call at all: histograms, records and slices travel as peer stores
+                self.peers.share_histogram(hist)
+                self.peers.barrier()
+                b.wc.partition_by_range_sum(self.peers.hist_slots(), self.world, self.world)
                 self._shuffle_peers(0, list(range(self.world)))
             else:
+                self.dist.all_reduce(hist, group=self.group)
+                b.partition_by_range(hist, self.world)
                 sent = self._shuffle(self.world, list(range(self.world)))
                 self.last_shuffle_bytes = sum(s for r, s in enumerate(sent) if r != self.rank)
             b.process()

@@ -195,7 +195,7 @@ def test_pack_straight_into_peer_slots(lb, P):
             c.close()
 
 
-def emulate_ordered(lb, data, P, via="concat", room=None, **kw):
+def emulate_ordered(lb, data, P, via="concat", room=None, hist_via="shared", **kw):
     """the ordered shuffle over P emulated ranks: parts are key ranges, every rank sorts its own
     range, rank 0 strings the slices together.  Returns rank 0's (keys, counts, vals) and the
     per-rank slices [(keys, counts)]."""
@@ -205,14 +205,24 @@ def emulate_ordered(lb, data, P, via="concat", room=None, **kw):
     keep = []
     try:
         hist = torch.zeros(lb.PARTITION_BINS, dtype=torch.int64, device="cuda")
+        slots = torch.zeros(P * lb.PARTITION_BINS, dtype=torch.int64, device="cuda")
+        own = [torch.zeros(lb.PARTITION_BINS, dtype=torch.int64, device="cuda") for _ in range(P)]
         torch.cuda.synchronize()
         for r, (lo, hi) in enumerate(shards):
             ctx[r].reset()
             ctx[r].map(dev[lo:hi])
-            ctx[r].partition_histogram(hist.data_ptr())        # every rank adds into the same array = the all-reduce
+            if hist_via == "shared":
+                ctx[r].partition_histogram(hist.data_ptr())    # every rank adds into the same array = the all-reduce
+            else:
+                # what ranks on one box do: own histogram put into slot r (of every rank; here one copy serves all)
+                ctx[r].partition_histogram(own[r].data_ptr())
+                ctx[r].peer_put([slots.data_ptr() + 8 * lb.PARTITION_BINS * r], own[r].data_ptr(), 8 * lb.PARTITION_BINS)
         torch.cuda.synchronize()
         for r in range(P):
-            ctx[r].partition_by_range(hist.data_ptr(), P)
+            if hist_via == "shared":
+                ctx[r].partition_by_range(hist.data_ptr(), P)
+            else:
+                ctx[r].partition_by_range_sum(slots.data_ptr(), P, P)
         inbox = [[] for _ in range(P)]
         for s in range(P):
             sizes = ctx[s].shuffle_sizes(P)
@@ -309,6 +319,41 @@ def test_ordered_shuffle_every_first_byte_and_tiny_inputs(lb):
         keys, counts, _, _, _ = emulate_ordered(lb, tiny, 4, table_log2=10)
         ref = pyoracle.wordcount(tiny)
         assert keys == ref.keys and counts == ref.counts
+
+
+@pytest.mark.parametrize("P", [2, 8])
+def test_ordered_shuffle_histograms_in_slots(lb, P):
+    from oracle import pyoracle
+    data = golden_input("hamlet") + b" " + golden_input("rand_longtok_s5")
+    keys, counts, _, slices, _ = emulate_ordered(lb, data, P, hist_via="slots", table_log2=14)
+    ref = pyoracle.wordcount(data)
+    assert keys == ref.keys and counts == ref.counts
+    same, _, _, slices2, _ = emulate_ordered(lb, data, P, table_log2=14)
+    assert [len(k) for k, _ in slices] == [len(k) for k, _ in slices2]      # the same ranges either way
+
+
+def test_peer_barrier_alone_and_put_to_many(lb):
+    """world = 1: the barrier only meets itself (on one GPU a kernel must not wait for another launch);
+    the two-rank case runs on real GPUs in bench.py --gpus 2 and tools/check_peer_exchange.py"""
+    c = lb.WordCount(device=0, table_log2=10)
+    try:
+        flags = torch.zeros(64, dtype=torch.int32, device="cuda")
+        src = torch.arange(4096, dtype=torch.int32, device="cuda")
+        dst = torch.zeros(3, 4096, dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        c.reset()
+        c.map(torch.frombuffer(bytearray(b"a b"), dtype=torch.uint8).cuda())
+        for epoch in (1, 2, 3):
+            c.peer_barrier([flags.data_ptr()], 0, 1, epoch)
+        c.peer_put([dst[i].data_ptr() for i in range(3)], src.data_ptr(), 4096 * 4)
+        c.process()
+        c.reduce()                                   # would report a barrier that timed out
+        assert int(flags[0].item()) == 3
+        assert bool((dst == src.unsqueeze(0)).all())
+        with pytest.raises(lb.LocustError):
+            c.peer_put([dst.data_ptr() + 4], src.data_ptr(), 64)          # unaligned destination
+    finally:
+        c.close()
 
 
 def test_range_parts_need_matching_nparts(lb):

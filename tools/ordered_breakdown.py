@@ -27,8 +27,9 @@ with torch.cuda.stream(st):
         dist.barrier(); torch.cuda.synchronize(); t = time.perf_counter()
         b.reset(); b.map(text); t = tick("map", t)
         hist = b.histogram(); t = tick("histogram", t)
-        dist.all_reduce(hist); t = tick("all_reduce(hist)", t)
-        b.partition_by_range(hist, world); t = tick("range map", t)
+        px.share_histogram(hist); t = tick("put histogram", t)
+        px.barrier(); t = tick("barrier0", t)
+        wc.partition_by_range_sum(px.hist_slots(), world, world); t = tick("range map", t)
         dst = [px.bufs[d][0] + rank * px.slot_bytes for d in range(world)]
         wc.shuffle_pack_peers(dst, px.slot_bytes, px.short_cap); t = tick("pack_peers", t)
         px.barrier(); t = tick("barrier", t)
