@@ -1,6 +1,8 @@
 #!/usr/bin/env python
-"""Run under torchrun on >= 2 GPUs: the fused pack+send path (IPC-mapped peer buffers, NVLink)
-and the NCCL all-to-all path must both give the oracle's result on rank 0."""
+"""Run under torchrun on >= 2 GPUs: every way of running a distributed job -- hash parts gathered
+on rank 0 or key-range parts sorted in place ("ordered"), over NCCL or over IPC-mapped peer
+buffers (NVLink), with the flag barrier or the all-reduce barrier -- must give the oracle's result
+on rank 0."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, torch.distributed as dist
@@ -23,21 +25,28 @@ wc = locust_b200.WordCount(device=lr, table_log2=log2, stream=st.cuda_stream)
 results = {}
 with torch.cuda.stream(st):
     px = PeerExchange(wc, dist, dev, 1 << log2)
-    for name, peers in (("nccl", None), ("peers", px), ("peers again", px)):
-        job = DistributedWordCount(GpuBackend(wc, dev), dist, peers=peers)
+    px_nccl_barrier = PeerExchange(wc, dist, dev, 1 << log2, flag_barrier=False)
+    for name, peers, ordered in (("gather nccl", None, False), ("gather peers", px, False), ("gather peers again", px, False),
+                                 ("ordered nccl", None, True), ("ordered peers", px, True), ("ordered peers again", px, True),
+                                 ("ordered peers, all-reduce barrier", px_nccl_barrier, True)):
+        job = DistributedWordCount(GpuBackend(wc, dev), dist, peers=peers, ordered=ordered)
         job.run(text)
-        results[name] = wc.result()[:2]
+        results[name] = (wc.result()[:2], ordered)
     px.close()
+    px_nccl_barrier.close()
 gathered = [None] * world
 dist.all_gather_object(gathered, bytes(text.cpu().numpy()))
 if rank == 0:
     from oracle import pyoracle
     ref = pyoracle.wordcount(b"".join(gathered), mode="fast", formats=False)
-    for name, (keys, counts) in results.items():
+    for name, ((keys, counts), _) in results.items():
         assert keys == ref.keys and counts == ref.counts, name
         print("%s: %d keys match the oracle" % (name, len(keys)))
 else:
-    for name, (keys, counts) in results.items():
-        assert keys == [] and counts == []
+    for name, ((keys, counts), ordered) in results.items():
+        if ordered:          # this rank kept the slice of its key range
+            assert keys == sorted(keys) and len(keys) > 0, name
+        else:
+            assert keys == [] and counts == [], name
 dist.destroy_process_group()
 print("rank %d ok" % rank)
