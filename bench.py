@@ -90,6 +90,30 @@ def workload(n_gpus):
                                         "delimiters across %d B200 (%d GiB per GPU), shuffle over NVLink" % (n_gpus, 16 // n_gpus))
 
 
+def bind_to_gpu_cpus(index):
+    """Runs this rank on the CPUs next to its GPU (NVML's affinity mask), so that the pinned staging
+    buffers of the end-to-end leg are allocated in that socket's memory and eight ranks do not pull
+    their input through one socket.  Returns the number of CPUs bound to, or None if it could not."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:                                            # CUDA_VISIBLE_DEVICES may renumber: go by UUID
+            import torch
+            h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(torch.cuda.get_device_properties(index).uuid)).encode())
+        except Exception:                               # noqa: BLE001
+            h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:                                   # noqa: BLE001 - an optimisation only
+        pass
+    return None
+
+
 def cpu_port_rate(sample, threads=1):
     """GB/s of the oracle's map -> sort -> run-length reduce (the reference's CPU stages) on `sample`."""
     from oracle import pyoracle
@@ -196,6 +220,7 @@ def main():
     locust_b200.load()
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa = bind_to_gpu_cpus(local_rank) if world > 1 else None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -384,6 +409,7 @@ def main():
                 "config": {"workload": desc, "bytes_per_gpu": per_gpu, "tokens_per_gpu": tokens if world == 1 else None,
                            "unique_keys": uniq, "table_log2": table_log2, "input_sha256": input_id,
                            "final_stage": (args.final if world > 1 else None),
+                           "cpus_bound_per_rank": numa,
                            "series": "N=1 is BASELINE config 2 (1 GiB, 50K vocab); N=2/4/8 are config 3 (16 GiB in total, "
                                      "1M vocab): total work is fixed from N=2 on",
                            "l2": "input per step (%d MiB per GPU) is larger than the 126 MB L2" % (per_gpu >> 20)},
