@@ -334,10 +334,25 @@ def main():
         # (B200_PROFILING.md); the shuffle here is latency-, not bandwidth-bound.
         sms_, sb_ = sum(x for x, _ in shuf) / len(shuf), sum(b for _, b in shuf) / len(shuf)
         if args.shuffle == "peers":
-            # fused pack+send: the packing kernel stores every record in the destination GPU's memory; no
-            # sizes are exchanged, so the bytes sent are not known on the host
-            shuffle = {"path": "peers (pack kernel writes over NVLink peer memory, one all-reduce barrier per exchange)",
-                       "ms": sms_, "bytes_sent_rank0": None, "achieved_gbs": None, "peak_gbs": 770.0, "frac": None}
+            # fused pack+send: the packing kernel stores every record in the destination GPU's memory and no
+            # sizes are exchanged, so the bytes that leave this rank are counted once here, outside the timing
+            with torch.cuda.stream(stream):
+                b = job.b
+                b.reset()
+                b.map(text)
+                if args.final == "ordered":
+                    hist = b.histogram()
+                    dist.all_reduce(hist)
+                    b.partition_by_range(hist, world)
+                sizes = b.shuffle_sizes(world)
+            sb_ = float(sum(x for r, x in enumerate(sizes) if r != rank))
+            shuffle = {"path": "peers (pack kernel writes over NVLink peer memory; the ranks' streams meet at flag "
+                               "barriers in peer memory)",
+                       "ms": sms_, "interval": "key histogram + its exchange + range map + pack/send + barrier + merge"
+                       if args.final == "ordered" else "both exchanges (hash shuffle, gather) with their barriers and merges",
+                       "bytes_sent_rank0": sb_, "achieved_gbs": sb_ / (sms_ * 1e-3) / GB if sms_ > 0 else None,
+                       "peak_gbs": 770.0, "frac": (sb_ / (sms_ * 1e-3) / GB / 770.0) if sms_ > 0 else None,
+                       "note": "latency bound: tens of MB per rank against a 770 GB/s link"}
         else:
             shuffle = {"path": "nccl (local pack, all_to_all_single of sizes and records)", "ms": sms_,
                        "bytes_sent_rank0": sb_, "achieved_gbs": sb_ / (sms_ * 1e-3) / GB if sms_ > 0 else None,
