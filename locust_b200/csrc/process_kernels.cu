@@ -166,6 +166,15 @@ __global__ void __launch_bounds__(256) sort_prep_kernel(const uint32_t *hist, ui
 // kStatic: tiles are dealt out by block index (tile = block, block + grid, ...) instead of by
 // ticket.  Only safe when every block of the grid is resident (cooperative launch): a tile waits
 // for lower-numbered tiles only, and those then belong to blocks that are running or done.
+// One 32-byte record = one 256-bit access (sm_100 has them; a record is one sector).
+LC_D ulonglong4 ld_rec(const Rec *p) {
+    ulonglong4 v;
+    asm volatile("ld.global.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(v.x), "=l"(v.y), "=l"(v.z), "=l"(v.w) : "l"(p));
+    return v;
+}
+LC_D void st_rec(Rec *p, const ulonglong4 &v) {
+    asm volatile("st.global.v4.u64 [%0], {%1,%2,%3,%4};" ::"l"(p), "l"(v.x), "l"(v.y), "l"(v.z), "l"(v.w) : "memory");
+}
 LC_D void sort_one_pass(const bool kStatic, const Records &r, const uint32_t *__restrict__ bases, unsigned long long n,
                         bool from_b, int pass, uint64_t *lb_state, uint32_t *ticket, uint32_t epoch) {
     __shared__ uint32_t wcnt[8][256];
@@ -188,7 +197,7 @@ LC_D void sort_one_pass(const bool kStatic, const Records &r, const uint32_t *__
         for (int i = 0; i < 8; ++i) {
             const unsigned long long e = tbase + i * 32u;
             const bool valid = e < n;
-            rec[i] = valid ? *reinterpret_cast<const ulonglong4 *>(src + e) : make_ulonglong4(0ull, 0ull, 0ull, 0ull);
+            rec[i] = valid ? ld_rec(src + e) : make_ulonglong4(0ull, 0ull, 0ull, 0ull);
             dg[i] = valid ? digit_of(rec[i].x, rec[i].y, pass) : 0x100u;
         }
 #pragma unroll
@@ -225,7 +234,7 @@ LC_D void sort_one_pass(const bool kStatic, const Records &r, const uint32_t *__
         for (int i = 0; i < 8; ++i) {
             if (dg[i] < 256u) {
                 const uint32_t pos = tile_base[dg[i]] + wcnt[w][dg[i]] + rk[i];
-                *reinterpret_cast<ulonglong4 *>(dst + pos) = rec[i];
+                st_rec(dst + pos, rec[i]);
             }
         }
         __syncthreads();
