@@ -139,6 +139,21 @@ LC_HD uint64_t hash_key128(uint64_t k0, uint64_t k1) {
     return mix64(k0 ^ (k1 * 0x9E3779B97F4A7C15ull) ^ (k1 >> 29));
 }
 
+// 32 bytes in one access: sm_100 has 256-bit global loads and stores, and the table slots and
+// the sort records are 32-byte aligned 32-byte structs (one memory sector each), so moving one
+// as a unit halves the load/store instructions and the sector requests of the 128-bit pairs the
+// compiler emits for a struct copy.  p must be 32-byte aligned.
+#if defined(__CUDACC__)
+__device__ __forceinline__ ulonglong4 ld256(const void *p) {
+    ulonglong4 v;
+    asm volatile("ld.global.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(v.x), "=l"(v.y), "=l"(v.z), "=l"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st256(void *p, const ulonglong4 &v) {
+    asm volatile("st.global.v4.u64 [%0], {%1,%2,%3,%4};" ::"l"(p), "l"(v.x), "l"(v.y), "l"(v.z), "l"(v.w) : "memory");
+}
+#endif
+
 // ---- global combiner table -------------------------------------------------
 // One slot = 32 bytes: key (k0, k1) = the token's bytes zero padded to 16,
 // little endian (k0 = bytes 0..7).  Tokens contain no NUL, so the padded value

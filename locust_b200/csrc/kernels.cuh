@@ -50,6 +50,18 @@ struct __align__(32) Rec {
 };
 
 // Double buffer of records for the sort; `longs` is the long-token list Rec::lidx points into.
+#if defined(__CUDACC__)
+__device__ __forceinline__ Rec load_rec(const Rec *p) {
+    const ulonglong4 v = ld256(p);
+    Rec r;
+    r.be0 = v.x; r.be1 = v.y; r.count = v.z; r.len = (uint32_t)v.w; r.lidx = (uint32_t)(v.w >> 32);
+    return r;
+}
+__device__ __forceinline__ void store_rec(Rec *p, const Rec &r) {
+    st256(p, make_ulonglong4(r.be0, r.be1, r.count, (unsigned long long)r.len | ((unsigned long long)r.lidx << 32)));
+}
+#endif
+
 struct Records {
     Rec *a, *b;
     const LongOcc *longs;

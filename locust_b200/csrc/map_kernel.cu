@@ -240,7 +240,7 @@ LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active
                 rec.be0 = bswap64((uint64_t)a | ((uint64_t)b << 32));
                 rec.be1 = bswap64((uint64_t)c | ((uint64_t)d << 32));
                 rec.count = 1ull; rec.len = L; rec.lidx = 0xFFFFFFFFu;
-                p.rec.a[e] = rec;
+                store_rec(p.rec.a + e, rec);
             } else {
                 atomicOr(&p.ctr->status, kStatusEntryFull);
             }
@@ -399,7 +399,7 @@ __global__ void __launch_bounds__(256) shuffle_merge_kernel(const uint8_t *__res
     const ulonglong4 *rec = reinterpret_cast<const ulonglong4 *>(part + 32);
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_short;
          i += (unsigned long long)gridDim.x * blockDim.x) {
-        const ulonglong4 v = rec[i];
+        const ulonglong4 v = ld256(rec + i);
         global_insert<false>(p, v.x, v.y, v.z);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {                      // long records are rare: one thread walks them

@@ -38,7 +38,7 @@ __global__ void __launch_bounds__(256) extract_kernel(const Slot *__restrict__ t
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const uint64_t i = first + j * 256u + threadIdx.x;
-            v[j] = i < slots ? *reinterpret_cast<const ulonglong4 *>(table + i) : make_ulonglong4(0ull, 0ull, 0ull, 0ull);
+            v[j] = i < slots ? ld256(table + i) : make_ulonglong4(0ull, 0ull, 0ull, 0ull);
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(256) extract_kernel(const Slot *__restrict__ t
                     Rec rec;
                     rec.be0 = bswap64(v[j].x); rec.be1 = bswap64(v[j].y); rec.count = v[j].z;
                     rec.len = key_len16(v[j].x, v[j].y); rec.lidx = 0xFFFFFFFFu;
-                    r.a[at] = rec;
+                    store_rec(r.a + at, rec);
                 } else {
                     atomicOr(&ctr->status, kStatusEntryFull);
                 }
@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(256) append_long_kernel(const LongOcc *__restr
         Rec rec;
         rec.be0 = b0; rec.be1 = b1; rec.count = t.count;
         rec.len = t.len > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)t.len; rec.lidx = (uint32_t)i;
-        r.a[e] = rec;
+        store_rec(r.a + e, rec);
     }
 }
 __global__ void bump_entries_kernel(uint64_t long_cap, uint64_t cap, Counters *ctr) {
@@ -166,15 +166,6 @@ __global__ void __launch_bounds__(256) sort_prep_kernel(const uint32_t *hist, ui
 // kStatic: tiles are dealt out by block index (tile = block, block + grid, ...) instead of by
 // ticket.  Only safe when every block of the grid is resident (cooperative launch): a tile waits
 // for lower-numbered tiles only, and those then belong to blocks that are running or done.
-// One 32-byte record = one 256-bit access (sm_100 has them; a record is one sector).
-LC_D ulonglong4 ld_rec(const Rec *p) {
-    ulonglong4 v;
-    asm volatile("ld.global.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(v.x), "=l"(v.y), "=l"(v.z), "=l"(v.w) : "l"(p));
-    return v;
-}
-LC_D void st_rec(Rec *p, const ulonglong4 &v) {
-    asm volatile("st.global.v4.u64 [%0], {%1,%2,%3,%4};" ::"l"(p), "l"(v.x), "l"(v.y), "l"(v.z), "l"(v.w) : "memory");
-}
 LC_D void sort_one_pass(const bool kStatic, const Records &r, const uint32_t *__restrict__ bases, unsigned long long n,
                         bool from_b, int pass, uint64_t *lb_state, uint32_t *ticket, uint32_t epoch) {
     __shared__ uint32_t wcnt[8][256];
@@ -197,7 +188,7 @@ LC_D void sort_one_pass(const bool kStatic, const Records &r, const uint32_t *__
         for (int i = 0; i < 8; ++i) {
             const unsigned long long e = tbase + i * 32u;
             const bool valid = e < n;
-            rec[i] = valid ? ld_rec(src + e) : make_ulonglong4(0ull, 0ull, 0ull, 0ull);
+            rec[i] = valid ? ld256(src + e) : make_ulonglong4(0ull, 0ull, 0ull, 0ull);
             dg[i] = valid ? digit_of(rec[i].x, rec[i].y, pass) : 0x100u;
         }
 #pragma unroll
@@ -234,7 +225,7 @@ LC_D void sort_one_pass(const bool kStatic, const Records &r, const uint32_t *__
         for (int i = 0; i < 8; ++i) {
             if (dg[i] < 256u) {
                 const uint32_t pos = tile_base[dg[i]] + wcnt[w][dg[i]] + rk[i];
-                st_rec(dst + pos, rec[i]);
+                st256(dst + pos, rec[i]);
             }
         }
         __syncthreads();
@@ -320,10 +311,10 @@ __global__ void __launch_bounds__(256) tie_fix_kernel(Records r, const Counters 
         while (j < n && s[j].be0 == a && s[j].be1 == b) ++j;
         // insertion sort of s[i..j) by full key
         for (unsigned long long x = i + 1; x < j; ++x) {
-            const Rec v = s[x];
+            const Rec v = load_rec(s + x);
             unsigned long long y = x;
             while (y > i) {
-                const Rec u = s[y - 1];
+                const Rec u = load_rec(s + y - 1);
                 if (cmp_tail(r, u, v) <= 0) break;
                 s[y] = u; --y;
             }

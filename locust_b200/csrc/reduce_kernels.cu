@@ -104,10 +104,10 @@ __global__ void __launch_bounds__(256) head_kernel(Records r, ReduceBufs o, cons
     const Rec *s = ctr->sort_parity != 0u ? r.b : r.a;
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
          i += (unsigned long long)gridDim.x * blockDim.x) {
-        const Rec cur = s[i];
+        const Rec cur = load_rec(s + i);
         bool head = true;
         if (i > 0) {
-            const Rec prev = s[i - 1];
+            const Rec prev = load_rec(s + i - 1);
             if (prev.be0 == cur.be0 && prev.be1 == cur.be1) {
                 if ((cur.be1 & 0xFFull) == 0ull) head = false;          // shorter than 16 bytes: prefix is the key
                 else head = !same_key(r, prev, cur);
@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(256) blob_kernel(Records r, ReduceBufs o, Coun
         const uint64_t off = o.key_offsets[k], len = o.key_offsets[k + 1] - off;
         if (off + len > o.blob_cap) { atomicOr(&ctr->status, kStatusBlobFull); continue; }
         uint8_t *dst = o.key_blob + off;
-        const Rec rec = s[pos];
+        const Rec rec = load_rec(s + pos);
         if (len <= 16) {
             for (uint32_t b = 0; b < (uint32_t)len; ++b)
                 dst[b] = (uint8_t)(b < 8 ? rec.be0 >> (56 - 8 * b) : rec.be1 >> (56 - 8 * (b - 8)));

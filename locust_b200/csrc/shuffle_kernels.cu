@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(256) shuffle_pack_kernel(const Slot *__restric
         __syncthreads();
         const uint64_t i = r * stride + tid;
         ulonglong4 v = make_ulonglong4(0ull, 0ull, 0ull, 0ull);
-        if (i < slots) v = *reinterpret_cast<const ulonglong4 *>(table + i);
+        if (i < slots) v = ld256(table + i);
         const bool occ = (v.x | v.y) != 0ull;
         uint32_t part = 0;
         unsigned long long local = 0;
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(256) shuffle_pack_kernel(const Slot *__restric
         __syncthreads();
         if (occ) {
             ulonglong4 *dst = reinterpret_cast<ulonglong4 *>(out + part_offsets[part] + 32ull) + sh_base[part] + local;
-            *dst = make_ulonglong4(v.x, v.y, v.z, 0ull);
+            st256(dst, make_ulonglong4(v.x, v.y, v.z, 0ull));
         }
         __syncthreads();
     }
@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(256) shuffle_pack_peers_kernel(const Slot *__r
         __syncthreads();
         const uint64_t i = r * stride + tid;
         ulonglong4 v = make_ulonglong4(0ull, 0ull, 0ull, 0ull);
-        if (i < slots) v = *reinterpret_cast<const ulonglong4 *>(table + i);
+        if (i < slots) v = ld256(table + i);
         const bool occ = (v.x | v.y) != 0ull;
         uint32_t part = 0;
         unsigned long long local = 0;
@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(256) shuffle_pack_peers_kernel(const Slot *__r
         __syncthreads();
         if (occ) {
             const unsigned long long at = sh_base[part] + local;
-            if (at < short_cap) reinterpret_cast<ulonglong4 *>(dst[part] + 32)[at] = make_ulonglong4(v.x, v.y, v.z, 0ull);
+            if (at < short_cap) st256(reinterpret_cast<ulonglong4 *>(dst[part] + 32) + at, make_ulonglong4(v.x, v.y, v.z, 0ull));
             else atomicOr(xflag, 1u);
         }
         __syncthreads();
