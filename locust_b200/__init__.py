@@ -194,11 +194,10 @@ class WordCount:
         self._check(self._L.locust_reduce(self._h), "locust_reduce")
 
     def run(self, data):
-        """reset + map + process + reduce."""
-        self.reset()
-        self.map(data)
-        self.process()
-        self.reduce()
+        """reset + map + process + reduce in one call (locust_wordcount)."""
+        ptr, n, where, keep = _ptr_of(data)
+        self._keep = [keep]                 # device inputs must outlive reduce()
+        self._check(self._L.locust_wordcount(self._h, ptr, n, where), "locust_wordcount")
         return self
 
     # -- results ------------------------------------------------------------------
