@@ -199,7 +199,8 @@ int locust_shuffle_merge(locust_ctx *ctx, const void *dev_records, uint64_t nbyt
  *
  * After locust_map on every rank:
  *   locust_partition_histogram adds, into dev_hist (device memory, uint64[LOCUST_PARTITION_BINS],
- *     zeroed by the caller), how many of this rank's keys start with each two-byte prefix;
+ *     zeroed by the caller), how many of this rank's keys start with each two-byte prefix (an
+ *     estimate from every eighth slot when the table is large: the counts only steer the balance);
  *   the caller sums dev_hist over all ranks (all-reduce);
  *   locust_partition_by_range builds the prefix -> part map from the summed histogram (the same
  *     on every rank): ranges follow key order and hold about the same number of keys, as far as

@@ -221,14 +221,17 @@ int launch_shuffle_pack_peers(const Slot *table, uint64_t slots, const LongOcc *
 
 
 // ---- ordered shuffle: key histogram and range map ----------------------------------------------
-// hist[bin] += number of this device's keys whose first two bytes are `bin` (65 536 bins).
+// hist[bin] += (an estimate of the) number of this device's keys whose first two bytes are `bin` (65 536 bins).
 __global__ void __launch_bounds__(256) partition_hist_kernel(const Slot *__restrict__ table, uint64_t slots,
                                                              const LongOcc *__restrict__ long_list, uint64_t long_cap,
                                                              const Counters *ctr, unsigned long long *hist) {
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < slots; i += stride) {
+    // The histogram only steers the balance of the ranges (any monotone map gives a correct result),
+    // so a large table is sampled: every eighth slot, which the hash fills like any other.
+    const uint64_t step = slots >= (1ull << 18) ? 8ull : 1ull;
+    for (uint64_t i = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * step; i < slots; i += stride * step) {
         const ulonglong2 k = *reinterpret_cast<const ulonglong2 *>(table + i);
-        if ((k.x | k.y) != 0ull) atomicAdd(&hist[bin_of_short(k.x)], 1ull);
+        if ((k.x | k.y) != 0ull) atomicAdd(&hist[bin_of_short(k.x)], step);
     }
     unsigned long long nl = ctr->n_long;
     if (nl > long_cap) nl = long_cap;
@@ -286,7 +289,8 @@ __global__ void __launch_bounds__(1024) partition_map_kernel(const unsigned long
 
 int launch_partition_hist(const Slot *table, uint64_t slots, const LongOcc *long_list, uint64_t long_cap,
                           const Counters *ctr, unsigned long long *hist, int num_sms, cudaStream_t st) {
-    partition_hist_kernel<<<grid_for(slots, num_sms), 256, 0, st>>>(table, slots, long_list, long_cap, ctr, hist);
+    partition_hist_kernel<<<grid_for(slots >= (1ull << 18) ? slots / 8 : slots, num_sms), 256, 0, st>>>(table, slots, long_list,
+                                                                                                       long_cap, ctr, hist);
     return 1;
 }
 int launch_partition_map(const unsigned long long *hist, uint32_t nhists, unsigned long long *sum_scratch,
