@@ -375,11 +375,41 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
     }
     drain_queue<kPlain>(p, wc, 1u);
     __syncthreads();
-    // flush the CTA's combiner into the global table
+    // Flush the CTA's combiner into the global table.  All 148 CTAs arrive here at about the same
+    // time with mostly the same keys, and a thread has a dozen slots to flush: done one after the
+    // other, every slot costs two or three L2 round trips (probe, claim, add).  So four slots go
+    // together: their home slots are read at once, the empty ones are claimed at once, and only a
+    // slot that turns out to be taken by another key takes the ordinary probing path.
     const unsigned long long *keys = reinterpret_cast<const unsigned long long *>(WC_SKEYS);
-    for (uint32_t i = threadIdx.x; i < kSmemSlots; i += kMapThreads) {
-        const unsigned long long k = keys[i];
-        if (k) global_insert<kPlain>(p, k, 0ull, (unsigned long long)WC_SCNT[i]);
+    constexpr uint32_t kFlush = 4;
+    for (uint32_t base = threadIdx.x; base < kSmemSlots; base += kMapThreads * kFlush) {
+        unsigned long long k[kFlush];
+        uint64_t o0[kFlush], o1[kFlush];
+        Slot *home[kFlush];
+        ulonglong2 cur[kFlush];
+#pragma unroll
+        for (uint32_t j = 0; j < kFlush; ++j) {
+            const uint32_t i = base + j * kMapThreads;
+            k[j] = i < kSmemSlots ? keys[i] : 0ull;
+            uint64_t h = hash_key128(k[j], 0ull);
+            if (!kPlain && (p.flags & LOCUST_F_WEAK_HASH)) h &= 0xFFull;
+            home[j] = p.table + (h & p.table_mask);
+            cur[j] = make_ulonglong2(0ull, 0ull);
+            if (k[j]) cur[j] = __ldcg(reinterpret_cast<const ulonglong2 *>(home[j]));
+        }
+#pragma unroll
+        for (uint32_t j = 0; j < kFlush; ++j) {
+            o0[j] = cur[j].x; o1[j] = cur[j].y;
+            if (k[j] && (cur[j].x | cur[j].y) == 0ull) cas128(home[j], k[j], 0ull, o0[j], o1[j]);     // returns what was there
+        }
+#pragma unroll
+        for (uint32_t j = 0; j < kFlush; ++j) {
+            if (!k[j]) continue;
+            const unsigned long long cnt = (unsigned long long)WC_SCNT[base + j * kMapThreads];
+            const bool claimed = (cur[j].x | cur[j].y) == 0ull && (o0[j] | o1[j]) == 0ull;        // our CAS went through
+            if (claimed || (o0[j] == k[j] && o1[j] == 0ull)) atomicAdd(&home[j]->count, cnt);
+            else global_insert<kPlain>(p, k[j], 0ull, cnt);
+        }
     }
 }
 
