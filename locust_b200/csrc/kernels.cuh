@@ -104,6 +104,9 @@ constexpr uint32_t kScanTile = 2048;
 
 cudaError_t map_kernel_setup();
 int launch_tokenize_combine(const MapParams &p, int num_sms, cudaStream_t st);
+// production MAP kernel (flags == 0), map_stream_kernel.cu; launch_tokenize_combine dispatches to it
+cudaError_t map_stream_setup();
+int launch_tokenize_stream(const MapParams &p, int variant, int num_sms, cudaStream_t st);
 
 // PROCESS
 int launch_extract(const Slot *table, uint64_t slots, Records r, Counters *ctr, int num_sms, cudaStream_t st);

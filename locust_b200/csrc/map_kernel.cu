@@ -17,6 +17,8 @@
 //      counted in a 2-way shared-memory table (exact 64-bit keys), misses and tokens
 //      of 9..16 bytes queued and inserted into the global table (exact 128-bit keys,
 //      128-bit CAS) 32 at a time; longer tokens are listed by address.
+#include <cstdlib>
+
 #include "kernels.cuh"
 #include "../../include/locust.h"
 
@@ -464,11 +466,21 @@ int launch_shuffle_merge(const uint8_t *part, uint64_t nbytes, MapParams p, int 
 cudaError_t map_kernel_setup() {
     cudaError_t e = cudaFuncSetAttribute(tokenize_combine_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(tokenize_combine_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    e = cudaFuncSetAttribute(tokenize_combine_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    if (e != cudaSuccess) return e;
+    return map_stream_setup();
+}
+
+// LOCUST_MAP_VARIANT (development switch): -1 = the register-staged kernel of this file for
+// flags == 0 too; 0.. = a configuration of the streaming kernel (map_stream_kernel.cu).
+static int map_variant() {
+    static const int v = [] { const char *s = getenv("LOCUST_MAP_VARIANT"); return s ? atoi(s) : 0; }();
+    return v;
 }
 
 int launch_tokenize_combine(const MapParams &p, int num_sms, cudaStream_t st) {
     if (p.hi <= p.lo) return 0;
+    if (p.flags == 0u && map_variant() >= 0) return launch_tokenize_stream(p, map_variant(), num_sms, st);
     const uint64_t nrows = ((p.hi + 511ull) >> 9) - (p.lo >> 9);
     uint64_t ctas = (nrows + kMapWarps - 1) / kMapWarps;
     if (ctas > (uint64_t)num_sms) ctas = (uint64_t)num_sms;
