@@ -144,6 +144,13 @@ int locust_map_intermediate(locust_ctx *ctx, const char *text, uint64_t nbytes);
  * what main.cu:408,:418,:468 print, but measured on the device. */
 float locust_stage_ms(locust_ctx *ctx, int stage);
 
+/* The cudaStream_t every call of this context enqueues its work on (cfg.stream, or the
+ * private stream locust_create made).  A caller that mixes liblocust calls with its own
+ * device work (a collective between locust_shuffle_pack and locust_shuffle_merge, say) issues
+ * that work on this stream, or orders its own stream against it with events.  No counterpart
+ * in the reference, which runs everything on the default stream (main.cu:403-472). */
+void *locust_stream(locust_ctx *ctx);
+
 /* Number of tokens counted (sum of all counts) and of kernels launched by the job
  * so far. */
 int locust_stats(locust_ctx *ctx, uint64_t *tokens, uint64_t *unique_keys, uint64_t *kernel_launches);

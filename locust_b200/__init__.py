@@ -23,7 +23,7 @@ EXPORTS = [
     "locust_version", "locust_create", "locust_destroy", "locust_reset", "locust_map",
     "locust_process", "locust_reduce", "locust_wordcount", "locust_result_host",
     "locust_result_device", "locust_format_result", "locust_stage_ms", "locust_stats",
-    "locust_last_error", "locust_shuffle_sizes", "locust_shuffle_pack",
+    "locust_last_error", "locust_stream", "locust_shuffle_sizes", "locust_shuffle_pack",
     "locust_shuffle_begin_merge", "locust_shuffle_merge", "locust_count_static",
     "locust_map_intermediate", "locust_exchange_alloc", "locust_ipc_export", "locust_ipc_open", "locust_ipc_close",
     "locust_shuffle_pack_peers", "locust_partition_histogram", "locust_partition_by_range",
@@ -77,6 +77,8 @@ def load():
     L.locust_stage_ms.argtypes = [vp, ctypes.c_int]
     L.locust_stage_ms.restype = ctypes.c_float
     L.locust_stats.argtypes = [vp, pp(u64), pp(u64), pp(u64)]
+    L.locust_stream.argtypes = [vp]
+    L.locust_stream.restype = ctypes.c_void_p
     L.locust_last_error.argtypes = [vp]
     L.locust_last_error.restype = ctypes.c_char_p
     L.locust_shuffle_sizes.argtypes = [vp, u32, pp(u64)]
@@ -171,6 +173,10 @@ class WordCount:
 
     def __exit__(self, *a):
         self.close()
+
+    def stream_ptr(self):
+        """the cudaStream_t (as an int) this context enqueues its work on"""
+        return self._L.locust_stream(self._h) or 0
 
     # -- stages (main.cu:406, :411-415, :447-465) -------------------------------
     def reset(self):

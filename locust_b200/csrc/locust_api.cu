@@ -591,6 +591,8 @@ int locust_stats(locust_ctx *c, uint64_t *tokens, uint64_t *unique_keys, uint64_
 
 const char *locust_last_error(locust_ctx *c) { return c ? c->err.c_str() : "null context"; }
 
+void *locust_stream(locust_ctx *c) { return c ? static_cast<void *>(c->stream) : nullptr; }
+
 // ---- intermediate text of multi mode (main.cu:66-103) -----------------------------------------
 int locust_map_intermediate(locust_ctx *c, const char *text, uint64_t nbytes) {
     if (!c || (!text && nbytes)) return LOCUST_E_ARG;

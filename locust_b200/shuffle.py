@@ -43,11 +43,20 @@ def plan_shards(data, nparts):
 
 
 class GpuBackend:
-    """liblocust.so + torch CUDA tensors."""
+    """liblocust.so + torch CUDA tensors.
+
+    liblocust enqueues on the context's own stream (locust_stream); torch's collectives and its
+    allocator order only against torch's *current* stream.  on_stream() makes the context's stream
+    torch's current one -- DistributedWordCount.run does everything inside it -- so that a
+    collective never reads a buffer the packing kernel is still writing."""
 
     def __init__(self, wc, device):
         import torch
         self.wc, self.device, self.torch = wc, device, torch
+        self.stream = torch.cuda.ExternalStream(wc.stream_ptr(), device=device)
+
+    def on_stream(self):
+        return self.torch.cuda.stream(self.stream)
 
     def alloc(self, nbytes):
         return self.torch.empty(max(int(nbytes), 32), dtype=self.torch.uint8, device=self.device)
@@ -271,6 +280,12 @@ class DistributedWordCount:
             b.result_concat(recvbuf, offsets, headers)
 
     def run(self, shard):
+        if hasattr(self.b, "on_stream"):
+            with self.b.on_stream():
+                return self._run(shard)
+        return self._run(shard)
+
+    def _run(self, shard):
         b = self.b
         b.reset()
         b.map(shard)

@@ -373,3 +373,50 @@ def test_range_parts_need_matching_nparts(lb):
         assert len(c.shuffle_sizes(2)) == 2
     finally:
         c.close()
+
+
+def test_distributed_wordcount_on_the_contexts_own_stream(lb):
+    """DistributedWordCount + GpuBackend with a default-constructed WordCount (private stream): the
+    collectives between pack and merge must be ordered against that stream, not torch's default one.
+    One rank (one GPU here), so the exchange is driven by hand: _shuffle packs, runs the NCCL
+    all-to-alls and merges, exactly as a multi-rank job does."""
+    import torch.distributed as dist
+    from oracle import pyoracle
+    from locust_b200.shuffle import DistributedWordCount, GpuBackend
+    made = False
+    if not dist.is_initialized():
+        dist.init_process_group("nccl", init_method="tcp://127.0.0.1:29591", rank=0, world_size=1,
+                                device_id=torch.device("cuda:0"))
+        made = True
+    try:
+        data = (golden_input("hamlet") + b" ") * 40
+        ref = pyoracle.wordcount(data)
+        dev = torch.frombuffer(bytearray(data), dtype=torch.uint8).cuda()
+        torch.cuda.synchronize()
+        for ordered in (False, True):
+            wc = lb.WordCount(device=0, table_log2=14)           # no stream given
+            b = GpuBackend(wc, torch.device("cuda:0"))
+            assert b.stream.cuda_stream == wc.stream_ptr() != 0
+            dwc = DistributedWordCount(b, dist, ordered=ordered)
+            for _ in range(3):
+                with b.on_stream():
+                    b.reset()
+                    b.map(dev)
+                    if ordered:
+                        hist = b.histogram()
+                        dist.all_reduce(hist)
+                        b.partition_by_range(hist, 1)
+                    dwc._shuffle(1, [0])
+                    b.process()
+                    b.reduce()
+                    if ordered:
+                        dwc._gather_results()
+                keys, counts, _ = wc.result()
+                assert keys == ref.keys and counts == ref.counts
+                dwc.run(dev)                                        # world 1: map, process, reduce
+                keys, counts, _ = wc.result()
+                assert keys == ref.keys and counts == ref.counts
+            wc.close()
+    finally:
+        if made:
+            dist.destroy_process_group()
