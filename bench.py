@@ -173,7 +173,8 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": desc},
+            "config": {"workload": desc + " [reference arm: timed on the first %d MiB of that text, one pass per step]"
+                                   % args.cpu_sample_mib},
             "cpu_baseline": {"value": value, "unit": "GB/s", "cores": 1, "kind": "port",
                              "sample": "first %d MiB of the workload text; map -> comparison sort of every token "
                                        "-> run-length reduce (oracle/wordcount_oracle.c), single thread like the "
@@ -189,7 +190,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="locust_b200", choices=["locust_b200", "reference"])
     ap.add_argument("--mib", type=int, default=0, help="override per-GPU input size (MiB); not the benchmark config")
-    ap.add_argument("--cpu-sample-mib", type=int, default=32)
+    ap.add_argument("--cpu-sample-mib", type=int, default=256,
+                    help="size of the text sample the CPU port is timed on (about 10 s of one core per pass at 256)")
     ap.add_argument("--table-log2", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--final", default="ordered", choices=["ordered", "gather"],
@@ -267,25 +269,27 @@ def main():
         torch.cuda.synchronize()
 
     def timed(buf, k):
-        """device time of k steps (ms, max over ranks) and the per-step map-kernel times"""
+        """device time of k steps (ms, max over ranks), the per-step map-kernel times, and the
+        per-step device times (events between steps; max over ranks per step)"""
         map_ms, shuf = [], []
         barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(k + 1)]
         with torch.cuda.stream(stream):
-            e0.record(stream)
-            for _ in range(k):
+            ev[0].record(stream)
+            for i in range(k):
                 step(buf)
+                ev[i + 1].record(stream)
                 map_ms.append(wc.stage_ms()[0])
                 if world > 1:
                     shuf.append((wc.shuffle_ms(), job.last_shuffle_bytes))
-            e1.record(stream)
         barrier()
-        ms = e0.elapsed_time(e1)
+        ms = ev[0].elapsed_time(ev[k])
+        per = [ev[i].elapsed_time(ev[i + 1]) for i in range(k)]
         if world > 1:
-            t = torch.tensor([ms], device=dev)
+            t = torch.tensor([ms] + per, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms, map_ms, shuf
+            ms, per = float(t[0].item()), [float(x) for x in t[1:].tolist()]
+        return ms, map_ms, shuf, per
 
     # ---- device-resident input ("value") ----------------------------------------------
     sampler = ClockSampler(local_rank)
@@ -295,7 +299,7 @@ def main():
         for _ in range(args.warmup):
             step(text)
     m0 = sampler.mark()
-    ms, map_ms, shuf = timed(text, args.steps)
+    ms, map_ms, shuf, step_ms = timed(text, args.steps)
     m1 = sampler.mark()
     st = wc.stats()
     stage_last = dict(zip(("map", "process", "reduce"), wc.stage_ms()))
@@ -386,22 +390,65 @@ def main():
            "d2h_bytes_per_step": d2h, "steps": e2e_steps,
            "note": "locust_map(LOCUST_HOST) from pinned memory, chunked copy overlapped with map; result copied to host"}
 
-    if world == 1:
-        # what the link delivers for the same bytes: a bare pinned host -> device copy, no word count
-        scratch = torch.empty(per_gpu, dtype=torch.uint8, device=dev)
-        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        with torch.cuda.stream(stream):
+    # what the host links deliver for the same bytes: a bare pinned host -> device copy on every rank at
+    # the same time, no word count (whole-job GB/s, slowest rank)
+    scratch = torch.empty(per_gpu, dtype=torch.uint8, device=dev)
+    with torch.cuda.stream(stream):
+        scratch.copy_(host, non_blocking=True)
+    barrier()
+    t0 = time.perf_counter()
+    with torch.cuda.stream(stream):
+        for _ in range(3):
             scratch.copy_(host, non_blocking=True)
-            c0.record(stream)
-            for _ in range(3):
-                scratch.copy_(host, non_blocking=True)
-            c1.record(stream)
-        torch.cuda.synchronize()
-        e2e["bare_h2d_copy_gbs"] = 3 * per_gpu / (c0.elapsed_time(c1) * 1e-3) / GB
-        e2e["frac_of_bare_copy"] = e2e["value"] / e2e["bare_h2d_copy_gbs"]
-        del scratch
+    barrier()
+    bare_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([bare_s], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        bare_s = float(t.item())
+    e2e["bare_h2d_copy_gbs"] = 3 * total / bare_s / GB
+    e2e["frac_of_bare_copy"] = e2e["value"] / e2e["bare_h2d_copy_gbs"]
+    del scratch
 
     clocks = sampler.stop(m0, m1)
+
+    # ---- parity of what was just timed, against the CPU oracle (outside every timed region) ----
+    import hashlib
+    import numpy as np
+    from oracle import parity as par
+    host_np = host.numpy()
+    chunk_sha = [hashlib.sha256(host_np[o:o + (1 << 30)]).hexdigest() for o in range(0, per_gpu, 1 << 30)]
+    t_par = time.perf_counter()
+    ref = par.oracle_arrays(host_np)                                  # this rank's shard, wc_oracle_fast
+    with torch.cuda.stream(stream):
+        wc.run(text)
+    single = wc.result_arrays()
+    my_tokens = wc.stats()["tokens"]
+    why = par.same_result(single, ref)
+    if why is None and my_tokens != ref[3]:
+        why = "tokens: got %d, oracle %d" % (my_tokens, ref[3])
+    if why:
+        sys.stderr.write("parity (rank %d, single GPU on its shard): %s\n" % (rank, why))
+    parity = {"oracle": "wc_oracle_fast (oracle/wordcount_oracle.c) on the full input of the timed steps",
+              "bytes_checked": total, "keys": int(len(ref[2])), "ok": why is None}
+    tokens_per_gpu, sha_all = [my_tokens], [chunk_sha]
+    if world > 1:
+        okt = torch.tensor([1 if why is None else 0], dtype=torch.int64, device=dev)
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+        tk = torch.zeros(world, dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(tk, torch.tensor([my_tokens], dtype=torch.int64, device=dev))
+        tokens_per_gpu = [int(x) for x in tk.tolist()]
+        sha_all = [None] * world
+        dist.all_gather_object(sha_all, chunk_sha)
+        with torch.cuda.stream(stream):
+            job.run(text)
+            res = wc.result_arrays()
+        chk = par.check_distributed(dist, dev, rank, world, ref[:3], res[:3], res if rank == 0 else None)
+        if rank == 0:
+            parity = dict(chk, bytes_checked=total, every_rank_alone_on_its_shard_equals_oracle=bool(okt.item()),
+                          ok=bool(chk["ok"] and okt.item()))
+    parity["seconds"] = time.perf_counter() - t_par
+    del ref, single
 
     # ---- the reference's CPU algorithm on this box's host cores (rank 0, N=1) -----------------
     cpu = None
@@ -414,27 +461,31 @@ def main():
                          "reduce, oracle/wordcount_oracle.c, single thread like the reference"
                          % (args.cpu_sample_mib, dt)}
         cpu["c1_reference"] = c1_reference(wc)
-        import hashlib
-        input_id = hashlib.sha256(host.numpy()).hexdigest()            # identity of the generated input
+        input_id = hashlib.sha256(host_np).hexdigest()                 # identity of the generated input
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+                "warmup": args.warmup, "ms_per_step": ms / args.steps,
+                "ms_per_step_median": sorted(step_ms)[len(step_ms) // 2], "ms_per_step_all": [round(x, 4) for x in step_ms],
+                "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-                "config": {"workload": desc, "bytes_per_gpu": per_gpu, "tokens_per_gpu": tokens if world == 1 else None,
+                "config": {"workload": desc, "bytes_per_gpu": per_gpu, "tokens_per_gpu": tokens_per_gpu,
                            "unique_keys": uniq, "table_log2": table_log2, "input_sha256": input_id,
+                           "input_sha256_per_gib_chunk_per_rank": sha_all,
                            "final_stage": (args.final if world > 1 else None),
                            "cpus_bound_per_rank": numa,
                            "series": "N=1 is BASELINE config 2 (1 GiB, 50K vocab); N=2/4/8 are config 3 (16 GiB in total, "
                                      "1M vocab): total work is fixed from N=2 on",
                            "l2": "input per step (%d MiB per GPU) is larger than the 126 MB L2" % (per_gpu >> 20)},
-                "roofline": roofline, "shuffle": shuffle, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
+                "roofline": roofline, "shuffle": shuffle, "cpu_baseline": cpu, "e2e": e2e, "parity": parity, "clocks": clocks,
                 "gpu_launches": launches_per_step * args.steps, "gpu_launches_per_step": launches_per_step,
                 "stage_ms_last_step": stage_last}
         print(json.dumps(line), flush=True)
     wc.close()
     if world > 1:
         dist.destroy_process_group()
+    if rank == 0 and not parity["ok"]:
+        sys.exit("bench.py: the timed result differs from the oracle: %s" % parity.get("why", "see stderr"))
 
 
 if __name__ == "__main__":

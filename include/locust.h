@@ -265,7 +265,7 @@ int locust_peer_barrier(locust_ctx *ctx, void *const *peer_flags, uint32_t rank,
  *
  * Limits (fixed, nothing grows): the input is at most LOCUST_STATIC_MAX_BYTES, it
  * holds at most LOCUST_STATIC_MAX_KEYS distinct words, and no word is longer than
- * 16 bytes.  A call beyond them fails with LOCUST_E_ARG (sizes passed in) or
+ * 16 bytes.  A call beyond them fails with LOCUST_E_ARG (nbytes passed in) or
  * LOCUST_E_CAPACITY (found while counting) and says why in errbuf.
  *
  *   dev_data, nbytes   input text in device memory of the current device
@@ -281,6 +281,10 @@ int locust_peer_barrier(locust_ctx *ctx, void *const *peer_flags, uint32_t rank,
  * Runs on the calling thread's current device.  The first call on a device also
  * does a one-time set-up (it resolves the address of the scratch array and sets a
  * kernel attribute); make that first call before any stream capture begins.
+ * Every call waits on the host until its work on `stream` has finished, because it
+ * reads the job counters back to decide between LOCUST_OK and LOCUST_E_CAPACITY.
+ * max_records beyond LOCUST_STATIC_MAX_KEYS is allowed (no more than that many
+ * records are ever written).
  * All calls on a device share the one scratch array: the table is cleared at the
  * start of every call, and two calls whose GPU work overlaps (different streams or
  * threads) race on it -- serialise them. */

@@ -16,23 +16,25 @@ constexpr uint32_t kStatusEntryFull = 4u;   // candidate-record buffers too smal
 constexpr uint32_t kStatusBlobFull  = 8u;   // key blob too small
 constexpr uint32_t kStatusTextFull  = 16u;  // formatted-text buffer too small
 
-// One entry of the long-token list: `count` occurrences of the key at ptr[0..len).
-// MAP writes one entry per occurrence (count 1); merged shuffle records carry sums.
+// One entry of the long-key list: `count` occurrences of the key at ptr[0..len), len > 16.
+// Entries are (all but) distinct keys: long_keys.cuh finds an existing entry through a hash
+// index and adds to its count.  hash = 64-bit hash of the key bytes.
 struct LongOcc {
     const uint8_t *ptr;
     uint64_t len;
     unsigned long long count;
-    uint64_t pad;
+    uint64_t hash;
 };
 
 // Device-side scalars of one job.
 struct Counters {
-    unsigned long long n_long;      // long-token occurrences seen (can exceed the buffer)
+    unsigned long long n_long;      // entries of the long-key list (can exceed the buffer: then kStatusLongFull)
     unsigned long long n_entries;   // candidate records after extract + append
     unsigned long long n_out;       // unique keys
     unsigned long long blob_bytes;  // sum of key lengths
     unsigned long long total;       // sum of counts = tokens
     unsigned long long text_bytes;  // formatted output size
+    unsigned long long n_tied;      // records whose 16-byte prefix is shared and that need ordering by their tails
     uint32_t status;
     uint32_t sort_parity;           // 0: sorted records in buffer A, 1: in buffer B
     uint32_t pass_active[16];       // radix pass p moves data
@@ -75,6 +77,8 @@ struct MapParams {
     uint64_t table_mask;        // slots - 1
     LongOcc *long_list;
     uint64_t long_cap;
+    uint32_t *long_index;       // open-addressed index over long_list: position + 1, 0 = empty
+    uint64_t long_index_mask;   // its slots - 1
     Counters *ctr;
     uint32_t flags;             // LOCUST_F_*
     Records rec;                // LOCUST_F_SORT_PATH only: every token becomes a record
@@ -85,6 +89,8 @@ struct SortScratch {
     uint32_t *bases;         // 16 * 256 exclusive bases
     uint64_t *lb_state;      // look-back words: tiles * 256
     uint32_t *tickets;       // pairs of {next tile, finished blocks}
+    uint32_t *tie_k, *tie_q; // positions of records with a shared 16-byte prefix: by key / by position
+    uint64_t tie_cap;        // their capacity (a power of two, >= 2 x long-key capacity)
 };
 
 struct ReduceBufs {
@@ -108,12 +114,15 @@ int launch_tokenize_combine(const MapParams &p, int num_sms, cudaStream_t st);
 cudaError_t map_stream_setup();
 int launch_tokenize_stream(const MapParams &p, int variant, int num_sms, cudaStream_t st);
 
+// zeroes the long-key index if the counters say the last job used it
+int launch_long_index_clear(const Counters *ctr, uint32_t *index, uint64_t slots, int num_sms, cudaStream_t st);
+
 // PROCESS
 int launch_extract(const Slot *table, uint64_t slots, Records r, Counters *ctr, int num_sms, cudaStream_t st);
 int launch_append_long(const LongOcc *list, uint64_t long_cap, Records r, Counters *ctr, int num_sms, cudaStream_t st);
 // epoch: first of 16 consecutive look-back epochs this sort may use
 int launch_sort_records(Records r, SortScratch s, Counters *ctr, uint32_t epoch, int num_sms, cudaStream_t st);
-int launch_tie_fix(Records r, Counters *ctr, int num_sms, cudaStream_t st);
+int launch_tie_fix(Records r, SortScratch s, Counters *ctr, int num_sms, cudaStream_t st);
 
 // REDUCE.  epoch: first of 3 consecutive epochs.
 int launch_reduce(Records r, SortScratch s, ReduceBufs o, Counters *ctr, uint32_t epoch, int num_sms, cudaStream_t st);

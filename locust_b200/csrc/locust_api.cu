@@ -43,6 +43,9 @@ struct locust_ctx {
     uint64_t slots = 0;
     LongOcc *long_list = nullptr;
     uint64_t long_cap = 0;
+    uint32_t *long_index = nullptr;   // hash index over long_list (long_keys.cuh)
+    uint64_t long_index_slots = 0;
+    bool long_index_dirty = true;     // freshly allocated: contents undefined
     Counters *ctr = nullptr;        // device
     Counters *h_ctr = nullptr;      // pinned host mirror
     Records rec{};
@@ -118,12 +121,21 @@ void free_record_buffers(locust_ctx *c) {
 int alloc_sized(locust_ctx *c, uint64_t slots, uint64_t long_cap) {
     cudaFree(c->table); c->table = nullptr;
     cudaFree(c->long_list); c->long_list = nullptr;
+    cudaFree(c->long_index); c->long_index = nullptr;
+    cudaFree(c->sort.tie_k); cudaFree(c->sort.tie_q); c->sort.tie_k = c->sort.tie_q = nullptr;
     free_record_buffers(c);
     c->slots = slots;
     c->long_cap = long_cap;
     const uint64_t cap = slots + long_cap;
     CU(dalloc(&c->table, slots));
     CU(dalloc(&c->long_list, long_cap));
+    c->long_index_slots = 4;
+    while (c->long_index_slots < 2 * long_cap) c->long_index_slots <<= 1;
+    CU(dalloc(&c->long_index, c->long_index_slots));
+    c->long_index_dirty = true;
+    c->sort.tie_cap = c->long_index_slots;          // >= 2 x long_cap: every long key and one 16-byte key per group
+    CU(dalloc(&c->sort.tie_k, c->sort.tie_cap));
+    CU(dalloc(&c->sort.tie_q, c->sort.tie_cap));
     CU(dalloc(&c->rec.a, cap)); CU(dalloc(&c->rec.b, cap));
     c->rec.longs = c->long_list;
     c->rec.cap = cap;
@@ -148,8 +160,20 @@ uint32_t take_epochs(locust_ctx *c, uint32_t k) {
     return e;
 }
 
+// The long-key index is zeroed for the next job only if the last one put anything into it
+// (decided on the device: the host does not know n_long without a synchronisation).
+cudaError_t clear_long_index(locust_ctx *c) {
+    if (c->long_index_dirty) {
+        c->long_index_dirty = false;
+        return cudaMemsetAsync(c->long_index, 0, c->long_index_slots * sizeof(uint32_t), c->stream);
+    }
+    c->launches += (uint64_t)launch_long_index_clear(c->ctr, c->long_index, c->long_index_slots, c->num_sms, c->stream);
+    return cudaGetLastError();
+}
+
 int clear_job(locust_ctx *c) {
     CU(cudaMemsetAsync(c->table, 0, c->slots * sizeof(Slot), c->stream));
+    CU(clear_long_index(c));                         // reads the previous job's counters: before they are zeroed
     CU(cudaMemsetAsync(c->ctr, 0, sizeof(Counters), c->stream));
     CU(cudaMemsetAsync(c->xflag, 0, sizeof(uint32_t), c->stream));
     c->cleared = true;
@@ -194,6 +218,8 @@ MapParams map_params(locust_ctx *c, const uint8_t *dev, uint64_t lo_abs, uint64_
     p.table_mask = c->slots - 1;
     p.long_list = c->long_list;
     p.long_cap = c->long_cap;
+    p.long_index = c->long_index;
+    p.long_index_mask = c->long_index_slots - 1;
     p.ctr = c->ctr;
     p.flags = c->flags;
     p.rec = c->rec;
@@ -250,7 +276,7 @@ int run_process(locust_ctx *c) {
     c->launches += (uint64_t)launch_extract(c->table, c->slots, c->rec, c->ctr, c->num_sms, c->stream);
     c->launches += (uint64_t)launch_append_long(c->long_list, c->long_cap, c->rec, c->ctr, c->num_sms, c->stream);
     c->launches += (uint64_t)launch_sort_records(c->rec, c->sort, c->ctr, take_epochs(c, 16), c->num_sms, c->stream);
-    c->launches += (uint64_t)launch_tie_fix(c->rec, c->ctr, c->num_sms, c->stream);
+    c->launches += (uint64_t)launch_tie_fix(c->rec, c->sort, c->ctr, c->num_sms, c->stream);
     CU(cudaGetLastError());
     CU(cudaEventRecord(c->ev[3], c->stream)); c->ev_set[3] = true;
     c->stage = 1;
@@ -275,7 +301,10 @@ int grow_and_remap(locust_ctx *c, uint32_t st) {
     if (st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull)) {
         uint64_t slots = c->slots, long_cap = c->long_cap;
         if (st & kStatusTableFull) slots *= 4;
-        if (st & kStatusLongFull) { long_cap = c->h_ctr->n_long + (c->h_ctr->n_long >> 3) + 1024; }
+        if (st & kStatusLongFull) {                  // n_long stops counting soon after the list is full: at least double
+            long_cap = c->h_ctr->n_long + (c->h_ctr->n_long >> 3) + 1024;
+            if (long_cap < 2 * c->long_cap) long_cap = 2 * c->long_cap;
+        }
         if (st & kStatusEntryFull) {
             // the record buffers hold slots + long_cap entries; n_entries kept counting past the end
             const uint64_t need = c->h_ctr->n_entries + c->h_ctr->n_long + 1024;
@@ -416,7 +445,8 @@ int locust_destroy(locust_ctx *c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     drop_segments(c);
     for (auto &sp : c->spares) cudaFree(sp.ptr);
-    cudaFree(c->table); cudaFree(c->long_list); cudaFree(c->ctr);
+    cudaFree(c->table); cudaFree(c->long_list); cudaFree(c->long_index); cudaFree(c->ctr);
+    cudaFree(c->sort.tie_k); cudaFree(c->sort.tie_q);
     free_record_buffers(c);
     cudaFree(c->sort.hist); cudaFree(c->sort.bases); cudaFree(c->sort.tickets);
     cudaFree(c->line_off); cudaFree(c->d_text); cudaFree(c->part_dev); cudaFree(c->xflag); cudaFree(c->partmap); cudaFree(c->peer_ptrs); cudaFree(c->hist_sum);
@@ -968,6 +998,7 @@ int locust_shuffle_begin_merge(locust_ctx *c) {
     if (c->stage != 0) return fail(c, LOCUST_E_STATE, "locust_shuffle_begin_merge after locust_process");
     CU(cudaSetDevice(c->device));
     CU(cudaMemsetAsync(c->table, 0, c->slots * sizeof(Slot), c->stream));
+    CU(clear_long_index(c));
     CU(cudaMemsetAsync(c->ctr, 0, sizeof(Counters), c->stream));
     c->cleared = true;
     c->shuffled = true;

@@ -20,6 +20,7 @@
 #include <cstdlib>
 
 #include "kernels.cuh"
+#include "long_keys.cuh"
 #include "../../include/locust.h"
 
 namespace locust {
@@ -144,9 +145,7 @@ __device__ __noinline__ void token_generic(const MapParams &p, const WarpCtx &wc
     if (L == 16 && L < maxlen && !is_delim(s[16])) {
         L = 17;
         while (L < maxlen && !is_delim(s[L])) ++L;
-        const unsigned long long idx = atomicAdd(&p.ctr->n_long, 1ull);
-        if (idx < p.long_cap) { p.long_list[idx].ptr = s; p.long_list[idx].len = L; p.long_list[idx].count = 1ull; }
-        else atomicOr(&p.ctr->status, kStatusLongFull);
+        long_insert(p, s, L, 1ull);
         return;
     }
     if (L <= 8 && (kPlain || wc.use_smem)) {
@@ -440,14 +439,7 @@ __global__ void __launch_bounds__(256) shuffle_merge_kernel(const uint8_t *__res
         while (done < long_bytes) {
             const unsigned long long len = reinterpret_cast<const unsigned long long *>(q + done)[0];
             const unsigned long long cnt = reinterpret_cast<const unsigned long long *>(q + done)[1];
-            const unsigned long long idx = atomicAdd(&p.ctr->n_long, 1ull);
-            if (idx < p.long_cap) {
-                p.long_list[idx].ptr = q + done + 16;
-                p.long_list[idx].len = len;
-                p.long_list[idx].count = cnt;
-            } else {
-                atomicOr(&p.ctr->status, kStatusLongFull);
-            }
+            long_insert(p, q + done + 16, len, cnt);             // the same key from several senders becomes one entry
             done += 16ull + ((len + 15ull) & ~15ull);
         }
     }

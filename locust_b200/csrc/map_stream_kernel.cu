@@ -32,6 +32,7 @@
 #include <type_traits>
 
 #include "kernels.cuh"
+#include "long_keys.cuh"
 #include "../../include/locust.h"
 
 namespace locust {
@@ -259,7 +260,7 @@ LC_D void insert_batches(const MapParams &p, const Table<kTok> &tab, const ulong
 }
 
 // Token longer than 16 bytes (or whose end lies beyond the 32-bit delimiter window) starting at
-// base[pos]: listed by address, one entry per occurrence.
+// base[pos]: counted in the long-key list (long_keys.cuh), found there by hash and full compare.
 __device__ __noinline__ void long_token(const MapParams &p, uint64_t pos) {
     const uint8_t *s = p.base + pos;
     const uint64_t maxlen = p.hi - pos;
@@ -273,9 +274,7 @@ __device__ __noinline__ void long_token(const MapParams &p, uint64_t pos) {
         if (L) global_probe(p, hash_key128(k0, k1) & p.table_mask, k0, k1, 1ull);
         return;
     }
-    const unsigned long long idx = atomicAdd(&p.ctr->n_long, 1ull);
-    if (idx < p.long_cap) { p.long_list[idx].ptr = s; p.long_list[idx].len = L; p.long_list[idx].count = 1ull; }
-    else atomicOr(&p.ctr->status, kStatusLongFull);
+    long_insert(p, s, L, 1ull);
 }
 
 // 16 bytes at byte offset `off` from base that straddle lo or hi: bytes outside [lo, hi) read as '\n'

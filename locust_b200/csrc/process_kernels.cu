@@ -296,10 +296,111 @@ LC_D int cmp_tail(const Records &r, const Rec &a, const Rec &b) {
     return la < lb ? -1 : (la > lb ? 1 : 0);
 }
 
-// A run of records with equal 16-byte prefix that holds keys of more than 16
-// bytes is put in full-key order by the thread that owns the run's first record.
+// Records that share their 16-byte prefix with a neighbour ("tied") are put in full-key order.
+// The radix sort has left them next to each other in arbitrary order; since the long-key list
+// holds distinct keys, a tied group has as many records as there are distinct keys with that
+// prefix (times the number of senders after a multi-GPU merge), which can still be millions
+// (URLs, paths, identifiers).  One cooperative launch:
+//   1. every tied record's position is appended to two arrays K and Q (order irrelevant);
+//   2. bitonic sort over both: K by full key (prefix, then the bytes behind it, then length),
+//      Q by position; the grid meets at a barrier after every compare-exchange step;
+//   3. the t-th smallest tied key belongs at the t-th smallest tied position (untied records do
+//      not lie inside a group, and groups are in prefix order already): records are gathered in
+//      key order into the spare record buffer and written back to the positions in Q.
+// A job without long keys leaves at the first test.
+LC_D int cmp_full(const Records &r, const Rec *recs, uint32_t a, uint32_t b) {
+    if (a == b) return 0;
+    if (a == 0xFFFFFFFFu) return 1;                  // padding sorts last
+    if (b == 0xFFFFFFFFu) return -1;
+    const Rec x = load_rec(recs + a), y = load_rec(recs + b);
+    if (x.be0 != y.be0) return x.be0 < y.be0 ? -1 : 1;
+    if (x.be1 != y.be1) return x.be1 < y.be1 ? -1 : 1;
+    return cmp_tail(r, x, y);
+}
+
+LC_D void grid_meet(uint32_t *bar, uint32_t &generation) {
+    ++generation;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(bar, 1u);
+        const uint32_t want = generation * gridDim.x;
+        uint32_t seen;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(bar) : "memory");
+            if (seen < want) __nanosleep(64);
+        } while (seen < want);
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(256) tie_sort_kernel(Records r, SortScratch sc, Counters *ctr, uint32_t *bar) {
+    if (*reinterpret_cast<volatile unsigned long long *>(&ctr->n_long) == 0ull) return;      // the same in every block
+    const unsigned long long n = ctr->n_entries;
+    Rec *recs = ctr->sort_parity != 0u ? r.b : r.a;
+    Rec *spare = ctr->sort_parity != 0u ? r.a : r.b;
+    uint32_t *K = sc.tie_k, *Q = sc.tie_q;
+    const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (uint64_t)gridDim.x * blockDim.x;
+    const uint32_t lane = threadIdx.x & 31u;
+    uint32_t generation = 0;
+    // 1. tied records
+    for (uint64_t i0 = tid - lane; i0 < n; i0 += nthreads) {
+        const uint64_t i = i0 + lane;
+        bool tied = false;
+        if (i < n) {
+            const ulonglong2 k = *reinterpret_cast<const ulonglong2 *>(recs + i);
+            if ((k.y & 0xFFull) != 0ull) {                                       // 16 bytes or more
+                if (i > 0) { const ulonglong2 q = *reinterpret_cast<const ulonglong2 *>(recs + i - 1); tied = q.x == k.x && q.y == k.y; }
+                if (!tied && i + 1 < n) { const ulonglong2 q = *reinterpret_cast<const ulonglong2 *>(recs + i + 1); tied = q.x == k.x && q.y == k.y; }
+            }
+        }
+        const uint32_t m = __ballot_sync(kFull, tied);
+        if (m) {
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(&ctr->n_tied, (unsigned long long)__popc(m));
+            base = __shfl_sync(kFull, base, 0);
+            if (tied) {
+                const unsigned long long at = base + __popc(m & ((1u << lane) - 1u));
+                if (at < sc.tie_cap) { K[at] = (uint32_t)i; Q[at] = (uint32_t)i; }
+                else atomicOr(&ctr->status, kStatusEntryFull);
+            }
+        }
+    }
+    grid_meet(bar, generation);
+    unsigned long long m;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(m) : "l"(&ctr->n_tied) : "memory");
+    if (m < 2ull || m > sc.tie_cap) return;
+    uint64_t M = 2;
+    while (M < m) M <<= 1;
+    for (uint64_t j = m + tid; j < M; j += nthreads) { K[j] = 0xFFFFFFFFu; Q[j] = 0xFFFFFFFFu; }
+    grid_meet(bar, generation);
+    // 2. bitonic sort of K (by key) and Q (by position)
+    for (uint64_t k = 2; k <= M; k <<= 1) {
+        for (uint64_t j = k >> 1; j > 0; j >>= 1) {
+            for (uint64_t i = tid; i < M; i += nthreads) {
+                const uint64_t l = i ^ j;
+                if (l <= i) continue;
+                const bool asc = (i & k) == 0;
+                const uint32_t ka = K[i], kb = K[l];
+                if ((cmp_full(r, recs, ka, kb) > 0) == asc) { K[i] = kb; K[l] = ka; }
+                const uint32_t qa = Q[i], qb = Q[l];
+                if ((qa > qb) == asc) { Q[i] = qb; Q[l] = qa; }
+            }
+            grid_meet(bar, generation);
+        }
+    }
+    // 3. into place
+    for (uint64_t j = tid; j < m; j += nthreads) st256(spare + j, ld256(recs + K[j]));
+    grid_meet(bar, generation);
+    for (uint64_t j = tid; j < m; j += nthreads) st256(recs + Q[j], ld256(spare + j));
+}
+
+// Fallback where a cooperative launch is not possible: the thread that owns the first record of a
+// tied run puts the run in order by insertion (fine for the short runs distinct long keys give).
 __global__ void __launch_bounds__(256) tie_fix_kernel(Records r, const Counters *ctr) {
     const unsigned long long n = ctr->n_entries;
+    if (ctr->n_long == 0ull) return;
     Rec *s = ctr->sort_parity != 0u ? r.b : r.a;
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i + 1 < n;
          i += (unsigned long long)gridDim.x * blockDim.x) {
@@ -309,7 +410,6 @@ __global__ void __launch_bounds__(256) tie_fix_kernel(Records r, const Counters 
         if (s[i + 1].be0 != a || s[i + 1].be1 != b) continue;               // run of one
         unsigned long long j = i + 2;
         while (j < n && s[j].be0 == a && s[j].be1 == b) ++j;
-        // insertion sort of s[i..j) by full key
         for (unsigned long long x = i + 1; x < j; ++x) {
             const Rec v = load_rec(s + x);
             unsigned long long y = x;
@@ -323,6 +423,13 @@ __global__ void __launch_bounds__(256) tie_fix_kernel(Records r, const Counters 
     }
 }
 
+__global__ void __launch_bounds__(256) long_index_clear_kernel(const Counters *ctr, uint32_t *index, uint64_t slots) {
+    if (ctr->n_long == 0ull) return;
+    uint4 *z = reinterpret_cast<uint4 *>(index);
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < slots / 4; i += (uint64_t)gridDim.x * blockDim.x)
+        z[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+
 // ---- host launchers -----------------------------------------------------------------
 static inline unsigned grid_for(uint64_t n, unsigned per_block, int num_sms, int blocks_per_sm) {
     uint64_t g = (n + per_block - 1) / per_block;
@@ -330,6 +437,11 @@ static inline unsigned grid_for(uint64_t n, unsigned per_block, int num_sms, int
     if (g > cap) g = cap;
     if (g < 1) g = 1;
     return (unsigned)g;
+}
+
+int launch_long_index_clear(const Counters *ctr, uint32_t *index, uint64_t slots, int num_sms, cudaStream_t st) {
+    long_index_clear_kernel<<<num_sms, 256, 0, st>>>(ctr, index, slots);
+    return 1;
 }
 
 int launch_extract(const Slot *table, uint64_t slots, Records r, Counters *ctr, int num_sms, cudaStream_t st) {
@@ -374,7 +486,23 @@ int launch_sort_records(Records r, SortScratch s, Counters *ctr, uint32_t epoch,
     return 18;
 }
 
-int launch_tie_fix(Records r, Counters *ctr, int num_sms, cudaStream_t st) {
+int launch_tie_fix(Records r, SortScratch sc, Counters *ctr, int num_sms, cudaStream_t st) {
+    static int resident_per_sm = -1;
+    if (resident_per_sm < 0) {
+        int nb = 0, coop = 0, dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, tie_sort_kernel, 256, 0) != cudaSuccess) nb = 0;
+        resident_per_sm = coop ? nb : 0;
+    }
+    if (resident_per_sm > 0 && sc.tie_k && sc.tie_q) {
+        unsigned g = (unsigned)num_sms * (unsigned)(resident_per_sm > 4 ? 4 : resident_per_sm);
+        uint32_t *bar = sc.hist + 16 * 256 + 1;          // zeroed with the histograms by launch_sort_records
+        void *args[] = {&r, &sc, &ctr, &bar};
+        if (cudaLaunchCooperativeKernel(reinterpret_cast<void *>(tie_sort_kernel), dim3(g), dim3(256), args, 0, st) == cudaSuccess)
+            return 1;
+        cudaGetLastError();
+    }
     tie_fix_kernel<<<grid_for(r.cap, 256, num_sms, 8), 256, 0, st>>>(r, ctr);
     return 1;
 }

@@ -75,11 +75,7 @@ extern "C" int locust_count_static(const void *dev_data, uint64_t nbytes, void *
         say(errbuf, errlen, "locust_count_static: input larger than LOCUST_STATIC_MAX_BYTES");
         return LOCUST_E_ARG;
     }
-    if (max_records > LOCUST_STATIC_MAX_KEYS) {
-        say(errbuf, errlen, "locust_count_static: max_records larger than LOCUST_STATIC_MAX_KEYS, the fixed scratch "
-                            "cannot hold that many distinct words");
-        return LOCUST_E_ARG;
-    }
+    if (max_records > LOCUST_STATIC_MAX_KEYS) max_records = LOCUST_STATIC_MAX_KEYS;   // a larger output buffer is harmless
     int dev = -1;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) { say(errbuf, errlen, "cudaGetDevice", e); return LOCUST_E_CUDA; }
