@@ -93,6 +93,11 @@ LC_D uint32_t atoms_add_ret(uint32_t a, uint32_t v) {
     asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(r) : "r"(a), "r"(v) : "memory");
     return r;
 }
+LC_D uint32_t atoms_cas32(uint32_t a, uint32_t cmp, uint32_t val) {
+    uint32_t r;
+    asm volatile("atom.shared.cas.b32 %0, [%1], %2, %3;" : "=r"(r) : "r"(a), "r"(cmp), "r"(val) : "memory");
+    return r;
+}
 LC_D unsigned long long atoms_cas64(uint32_t a, unsigned long long cmp, unsigned long long val) {
     unsigned long long r;
     asm volatile("atom.shared.cas.b64 %0, [%1], %2, %3;" : "=l"(r) : "r"(a), "l"(cmp), "l"(val) : "memory");
@@ -487,12 +492,20 @@ __global__ void __launch_bounds__((kTok + kIns) * 32, 1) tokenize_stream_kernel(
                     // the top 32 queued keys go to an inserter warp, or are inserted here when the ring is full
                     while (qn >= 32u) {
                         __syncwarp();
-                        const uint32_t head = lds32(xb + oXHead), tail = lds32(xb + oXTail);
                         const uint32_t src = wa + oQueue + 16u * (qn - 32u) + 16u * lane;
-                        if (kIns > 0 && head - tail < kXSlots) {
-                            uint32_t idx = 0;
-                            if (lane == 0) idx = atoms_add_ret(xb + oXHead, 1u);
+                        // a place in the ring is taken only while fewer than kXSlots batches are outstanding (compare-and-swap on
+                        // the head: the barriers' phase parity cannot tell use k of a slot from use k + 2)
+                        uint32_t idx = 0, got = 0;
+                        if (kIns > 0) {
+                            if (lane == 0) {
+                                idx = lds32(xb + oXHead);
+                                const uint32_t tail = lds32(xb + oXTail);
+                                if (idx - tail < kXSlots) got = atoms_cas32(xb + oXHead, idx, idx + 1u) == idx ? 1u : 0u;
+                            }
+                            got = __shfl_sync(kFull, got, 0);
                             idx = __shfl_sync(kFull, idx, 0);
+                        }
+                        if (got) {
                             const uint32_t s = idx % kXSlots, round = idx / kXSlots;
                             mbar_wait(xb + oXEmpty + 8 * s, (round & 1u) ^ 1u);
                             const uint4 kk = lds128(src);
