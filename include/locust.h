@@ -166,6 +166,12 @@ const char *locust_last_error(locust_ctx *ctx);
  * bytes_per_part: host array of nparts. */
 int locust_shuffle_sizes(locust_ctx *ctx, uint32_t nparts, uint64_t *bytes_per_part);
 
+/* The two numbers behind each bytes_per_part of the last locust_shuffle_sizes call: short
+ * records (keys of <= 16 bytes, 32 bytes each) and bytes of long records per part.  A caller
+ * that sizes the receive slots of locust_shuffle_pack_peers from the counts instead of from
+ * the sender's table size needs them separately (short_cap, and slot_bytes - 32 - 32 * short_cap). */
+int locust_shuffle_counts(locust_ctx *ctx, uint32_t nparts, uint64_t *short_records, uint64_t *long_bytes);
+
 /* Packs part p at dev_out + part_offsets[p] (device memory, caller-owned; offsets
  * and sizes as reported by locust_shuffle_sizes, each a multiple of 32). */
 int locust_shuffle_pack(locust_ctx *ctx, uint32_t nparts, void *dev_out, const uint64_t *part_offsets);
@@ -249,6 +255,38 @@ int locust_result_adopt_slots(locust_ctx *ctx, const void *dev_slots, uint64_t s
 int locust_peer_put(locust_ctx *ctx, uint32_t ndst, void *const *dsts, const void *dev_src, uint64_t nbytes);
 int locust_partition_by_range_sum(locust_ctx *ctx, const void *dev_hists, uint32_t nhists, uint32_t nparts);
 int locust_peer_barrier(locust_ctx *ctx, void *const *peer_flags, uint32_t rank, uint32_t world, uint32_t epoch);
+
+/* ---- several GPUs of one box from one process -----------------------------------
+ * Replaces the reference's multi mode as a whole: the per-node line windows and stage
+ * arguments of its command line (main.cu:367-385), the sorted partials handed over in
+ * /tmp/out.txt (:421-446) and the command runner that starts the nodes
+ * (Distributor/slave.py:30-32).  One call runs the job on every listed GPU: shards cut on
+ * delimiters, map on every GPU, two-byte-prefix histograms and range map, records packed
+ * straight into the owning GPU's memory (NVLink peer stores; receive slots sized from a
+ * count pass, so a table that overflowed in MAP still grows), merge + PROCESS + REDUCE per
+ * key range, sorted slices strung together on devices[0].  One host thread per GPU; the
+ * streams meet through events, never through kernels that wait for each other, so the same
+ * device may be listed several times (devices = {0, 0, 0} runs three ranks on GPU 0).
+ *
+ *   locust_multi_create            contexts, streams and peer access for devices[0..n)
+ *                                  (cfg->device and cfg->stream are ignored; NULL cfg = defaults)
+ *   locust_multi_wordcount         host_data[0..nbytes): cut, copied and counted; the result is
+ *                                  on locust_multi_context(m, 0)
+ *   locust_multi_wordcount_device  shard r already lies in device memory of devices[r]; every shard
+ *                                  must begin at a token boundary and stay valid until the next job
+ *   locust_multi_context           the per-rank context: rank 0 for locust_result_host /
+ *                                  locust_result_device / locust_format_result after a job, any rank
+ *                                  for locust_stage_ms / locust_stats
+ *   locust_multi_stats             device time of the last job on rank 0's stream (first kernel to
+ *                                  result in place, ms) and the record bytes that left their GPU */
+typedef struct locust_multi locust_multi;
+int locust_multi_create(const int *devices, int n, const locust_config *cfg, locust_multi **out);
+int locust_multi_destroy(locust_multi *m);
+int locust_multi_wordcount(locust_multi *m, const void *host_data, uint64_t nbytes);
+int locust_multi_wordcount_device(locust_multi *m, const void *const *dev_shards, const uint64_t *nbytes);
+locust_ctx *locust_multi_context(locust_multi *m, int rank);
+int locust_multi_stats(locust_multi *m, float *job_ms, uint64_t *record_bytes_exchanged);
+const char *locust_multi_last_error(locust_multi *m);
 
 /* ---- for callers that cannot allocate ------------------------------------------
  * No counterpart in the reference (its main() allocates freely, main.cu:393,:402,:451).

@@ -29,7 +29,9 @@ EXPORTS = [
     "locust_shuffle_pack_peers", "locust_partition_histogram", "locust_partition_by_range",
     "locust_result_part_bytes", "locust_result_part_pack", "locust_result_concat",
     "locust_result_header", "locust_result_adopt_slots", "locust_peer_put", "locust_partition_by_range_sum",
-    "locust_peer_barrier",
+    "locust_peer_barrier", "locust_shuffle_counts",
+    "locust_multi_create", "locust_multi_destroy", "locust_multi_wordcount", "locust_multi_wordcount_device",
+    "locust_multi_context", "locust_multi_stats", "locust_multi_last_error",
 ]
 PARTITION_BINS = 65536
 STATIC_MAX_KEYS = 16384
@@ -82,6 +84,16 @@ def load():
     L.locust_last_error.argtypes = [vp]
     L.locust_last_error.restype = ctypes.c_char_p
     L.locust_shuffle_sizes.argtypes = [vp, u32, pp(u64)]
+    L.locust_shuffle_counts.argtypes = [vp, u32, pp(u64), pp(u64)]
+    L.locust_multi_create.argtypes = [pp(ctypes.c_int), ctypes.c_int, vp, pp(vp)]
+    L.locust_multi_destroy.argtypes = [vp]
+    L.locust_multi_wordcount.argtypes = [vp, vp, u64]
+    L.locust_multi_wordcount_device.argtypes = [vp, pp(vp), pp(u64)]
+    L.locust_multi_context.argtypes = [vp, ctypes.c_int]
+    L.locust_multi_context.restype = vp
+    L.locust_multi_stats.argtypes = [vp, pp(ctypes.c_float), pp(u64)]
+    L.locust_multi_last_error.argtypes = [vp]
+    L.locust_multi_last_error.restype = ctypes.c_char_p
     L.locust_shuffle_pack.argtypes = [vp, u32, vp, pp(u64)]
     L.locust_shuffle_begin_merge.argtypes = [vp]
     L.locust_shuffle_merge.argtypes = [vp, vp, u64]
@@ -352,3 +364,73 @@ class WordCount:
         if keepalive is not None:
             self._keep.append(keepalive)
         self._check(self._L.locust_shuffle_merge(self._h, dev_ptr, nbytes), "locust_shuffle_merge")
+
+
+class MultiWordCount:
+    """locust_multi_*: one job over several GPUs of one box, driven from this process.  The reference's
+    multi mode (main.cu:367-385, :421-446; Distributor/slave.py) as one call; the result is read through
+    the rank-0 context (result(), result_arrays(), format(), stats() as on WordCount)."""
+
+    def __init__(self, devices, table_log2=0, flags=0, long_capacity=0):
+        L = load()
+        self._L = L
+        devs = (ctypes.c_int * len(devices))(*devices)
+        cfg = _Config(0, table_log2, flags, 0, long_capacity, None)
+        h = ctypes.c_void_p()
+        rc = L.locust_multi_create(devs, len(devices), ctypes.byref(cfg), ctypes.byref(h))
+        self._h, self.devices = h, list(devices)
+        if rc != 0:
+            msg = L.locust_multi_last_error(h).decode() if h else "no handle"
+            if h:
+                L.locust_multi_destroy(h)
+            self._h = None
+            raise LocustError("locust_multi_create failed (%d): %s" % (rc, msg))
+        self._keep = None
+
+    def _check(self, rc, what):
+        if rc != 0:
+            e = LocustError("%s failed (%d): %s" % (what, rc, self._L.locust_multi_last_error(self._h).decode()))
+            e.code = rc
+            raise e
+
+    def context(self, rank=0):
+        """a WordCount view of rank's context (borrowed: closing it does nothing)"""
+        wc = WordCount.__new__(WordCount)
+        wc._L, wc._h, wc._keep = self._L, ctypes.c_void_p(self._L.locust_multi_context(self._h, rank)), []
+        wc.close = lambda: None
+        return wc
+
+    def run(self, data):
+        """host bytes (bytes, numpy uint8 array, pinned CPU tensor): cut on delimiters, one shard per GPU"""
+        ptr, n, where, keep = _ptr_of(data)
+        if where != HOST:
+            raise LocustError("MultiWordCount.run takes host memory; use run_shards for device-resident shards")
+        self._keep = keep
+        self._check(self._L.locust_multi_wordcount(self._h, ptr, n), "locust_multi_wordcount")
+        return self.context(0)
+
+    def run_shards(self, tensors):
+        """one contiguous CUDA uint8 tensor per rank, already on that rank's device"""
+        n = len(self.devices)
+        assert len(tensors) == n
+        ptrs = (ctypes.c_void_p * n)(*[t.data_ptr() for t in tensors])
+        sizes = (ctypes.c_uint64 * n)(*[t.numel() for t in tensors])
+        self._keep = list(tensors)
+        self._check(self._L.locust_multi_wordcount_device(self._h, ptrs, sizes), "locust_multi_wordcount_device")
+        return self.context(0)
+
+    def stats(self):
+        ms, b = ctypes.c_float(), ctypes.c_uint64()
+        self._L.locust_multi_stats(self._h, ctypes.byref(ms), ctypes.byref(b))
+        return {"job_ms": ms.value, "record_bytes_exchanged": b.value}
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.locust_multi_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

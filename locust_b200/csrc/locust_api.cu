@@ -730,6 +730,14 @@ int locust_shuffle_sizes(locust_ctx *c, uint32_t nparts, uint64_t *bytes_per_par
     return LOCUST_OK;
 }
 
+int locust_shuffle_counts(locust_ctx *c, uint32_t nparts, uint64_t *short_records, uint64_t *long_bytes) {
+    if (!c || nparts == 0 || !short_records || !long_bytes) return LOCUST_E_ARG;
+    if (c->part_n != nparts || c->part_host.size() < 2ull * nparts)
+        return fail(c, LOCUST_E_STATE, "locust_shuffle_counts needs locust_shuffle_sizes with the same nparts first");
+    for (uint32_t i = 0; i < nparts; ++i) { short_records[i] = c->part_host[i]; long_bytes[i] = c->part_host[nparts + i]; }
+    return LOCUST_OK;
+}
+
 int locust_shuffle_pack(locust_ctx *c, uint32_t nparts, void *dev_out, const uint64_t *part_offsets) {
     if (!c || !dev_out || !part_offsets || nparts == 0) return LOCUST_E_ARG;
     if (c->stage != 0 || c->part_n != nparts) return fail(c, LOCUST_E_STATE, "locust_shuffle_pack needs locust_shuffle_sizes with the same nparts first");

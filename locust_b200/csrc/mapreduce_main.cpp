@@ -15,6 +15,11 @@
 // which holds one line per token -- and reduces it.  Inside one box the NCCL shuffle of
 // liblocust replaces this file hand-off; the stages are kept so the binary still fits the
 // reference's launcher (Distributor/slave.py starts it with these arguments).
+//
+// LOCUST_DEVICES=0,1,2,...  (single mode) runs the job on several GPUs of the box through
+// locust_multi_*: the file is cut on delimiters, one shard per listed device, and the records are
+// exchanged over NVLink -- what the reference's launcher + line windows + /tmp/out.txt do across
+// machines.  The stdout is the same as on one GPU.
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -139,6 +144,49 @@ int main(int argc, char *argv[]) {
         return 1;
     }
     printf("Length: %i\n", (int)nlines);
+
+    if (const char *devs = getenv("LOCUST_DEVICES")) {
+        if (stage != 0) { fprintf(stderr, "MapReduce: LOCUST_DEVICES applies to single mode only\n"); return 2; }
+        std::vector<int> devices;
+        for (const char *q = devs; *q;) {
+            char *end = nullptr;
+            const long v = strtol(q, &end, 10);
+            if (end == q) break;
+            devices.push_back((int)v);
+            q = (*end == ',') ? end + 1 : end;
+        }
+        if (devices.empty()) { fprintf(stderr, "MapReduce: LOCUST_DEVICES holds no device number\n"); return 2; }
+        locust_multi *m = nullptr;
+        int rcm = locust_multi_create(devices.data(), (int)devices.size(), &cfg, &m);
+        if (rcm == LOCUST_OK) rcm = locust_multi_wordcount(m, buf + lo, hi - lo);
+        if (rcm != LOCUST_OK) {
+            fprintf(stderr, "MapReduce: multi-GPU job failed (%d): %s\n", rcm, m ? locust_multi_last_error(m) : "");
+            if (m) locust_multi_destroy(m);
+            return 1;
+        }
+        // stage times: the slowest rank's, as a launcher waiting for every node would see them
+        float t_map = 0.f, t_proc = 0.f, t_red = 0.f;
+        for (int r = 0; r < (int)devices.size(); ++r) {
+            locust_ctx *cr = locust_multi_context(m, r);
+            const float a = locust_stage_ms(cr, LOCUST_STAGE_MAP), b = locust_stage_ms(cr, LOCUST_STAGE_PROCESS), c = locust_stage_ms(cr, LOCUST_STAGE_REDUCE);
+            if (a > t_map) t_map = a;
+            if (b > t_proc) t_proc = b;
+            if (c > t_red) t_red = c;
+        }
+        printf("GPU mapping %d nanoseconds \n", (int)(t_map * 1e6f));
+        printf("GPU stream compaction and sorting %d nanoseconds \n", (int)(t_proc * 1e6f));
+        printf("GPU reduce %d nanoseconds \n", (int)(t_red * 1e6f));
+        const char *text = nullptr;
+        uint64_t nbytes = 0;
+        locust_ctx *c0 = locust_multi_context(m, 0);
+        rcm = locust_format_result(c0, key_format, &text, &nbytes);
+        if (rcm) { fprintf(stderr, "MapReduce: locust_format_result failed (%d): %s\n", rcm, locust_last_error(c0)); return 1; }
+        fwrite(text, 1, nbytes, stdout);
+        locust_multi_destroy(m);
+        cudaFreeHost(buf);
+        printf("\nDone\n");
+        return 0;
+    }
 
     locust_ctx *ctx = nullptr;
     int rc = locust_create(&cfg, &ctx);
