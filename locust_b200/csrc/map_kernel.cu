@@ -463,10 +463,11 @@ cudaError_t map_kernel_setup() {
     return map_stream_setup();
 }
 
-// LOCUST_MAP_VARIANT (development switch): -1 = the register-staged kernel of this file for
-// flags == 0 too; 0.. = a configuration of the streaming kernel (map_stream_kernel.cu).
+// LOCUST_MAP_VARIANT (development switch): -1 (default) = the register-staged kernel of this file;
+// 0.. = a configuration of the streaming kernel (map_stream_kernel.cu: bulk-async row ring, inserter
+// warps), which is correct on every test but measured slower.
 static int map_variant() {
-    static const int v = [] { const char *s = getenv("LOCUST_MAP_VARIANT"); return s ? atoi(s) : 0; }();
+    static const int v = [] { const char *s = getenv("LOCUST_MAP_VARIANT"); return s ? atoi(s) : -1; }();
     return v;
 }
 

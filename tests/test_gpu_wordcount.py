@@ -433,3 +433,14 @@ def test_larger_configs_by_properties(lb, name, mib, log2):
     sums = np.add.reduceat(c, np.flatnonzero(head))
     assert (k[head] == kw).all() and (sums == cw).all()
     wc.close()
+
+
+def test_streaming_map_kernel_variants(lb):
+    """the bulk-async / inserter-warp MAP kernel (LOCUST_MAP_VARIANT >= 0, map_stream_kernel.cu) is not the
+    default, but it stays correct: a ladder of inputs through it in child processes, against the oracle"""
+    import sys
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "dbg_map.py"), "0,3", "60", "small"],
+                         capture_output=True, text=True, timeout=900).stdout
+    lines = [l for l in out.splitlines() if l.startswith("variant")]
+    assert len(lines) >= 16, out
+    assert all(": ok " in l for l in lines), out
