@@ -191,6 +191,9 @@ int locust_shuffle_pack(locust_ctx *ctx, uint32_t nparts, void *dev_out, const u
  * locust_ipc_export / _open / _close: the 64-byte handle another process on the same box needs
  * to map that buffer (cudaIpcGetMemHandle / OpenMemHandle / CloseMemHandle). */
 int locust_exchange_alloc(locust_ctx *ctx, uint64_t nbytes, void **dev_buf);
+/* Gives a buffer of locust_exchange_alloc back before the context is destroyed (a caller that re-sizes
+ * its receive slots); peers must have closed their mappings of it. */
+int locust_exchange_free(locust_ctx *ctx, void *dev_buf);
 int locust_ipc_export(locust_ctx *ctx, const void *dev_buf, uint8_t handle[64]);
 int locust_ipc_open(locust_ctx *ctx, const uint8_t handle[64], void **dev_buf);
 int locust_ipc_close(locust_ctx *ctx, void *dev_buf);

@@ -29,7 +29,7 @@ EXPORTS = [
     "locust_shuffle_pack_peers", "locust_partition_histogram", "locust_partition_by_range",
     "locust_result_part_bytes", "locust_result_part_pack", "locust_result_concat",
     "locust_result_header", "locust_result_adopt_slots", "locust_peer_put", "locust_partition_by_range_sum",
-    "locust_peer_barrier", "locust_shuffle_counts",
+    "locust_peer_barrier", "locust_shuffle_counts", "locust_exchange_free",
     "locust_multi_create", "locust_multi_destroy", "locust_multi_wordcount", "locust_multi_wordcount_device",
     "locust_multi_context", "locust_multi_stats", "locust_multi_last_error",
 ]
@@ -99,6 +99,7 @@ def load():
     L.locust_shuffle_merge.argtypes = [vp, vp, u64]
     L.locust_map_intermediate.argtypes = [vp, ctypes.c_char_p, u64]
     L.locust_exchange_alloc.argtypes = [vp, u64, pp(vp)]
+    L.locust_exchange_free.argtypes = [vp, vp]
     L.locust_ipc_export.argtypes = [vp, vp, ctypes.c_char_p]
     L.locust_ipc_open.argtypes = [vp, ctypes.c_char_p, pp(vp)]
     L.locust_ipc_close.argtypes = [vp, vp]
@@ -285,6 +286,12 @@ class WordCount:
         self._check(self._L.locust_shuffle_sizes(self._h, nparts, arr), "locust_shuffle_sizes")
         return list(arr)
 
+    def shuffle_counts(self, nparts):
+        """(short records per part, bytes of long records per part) of the last shuffle_sizes call"""
+        a, b = (ctypes.c_uint64 * nparts)(), (ctypes.c_uint64 * nparts)()
+        self._check(self._L.locust_shuffle_counts(self._h, nparts, a, b), "locust_shuffle_counts")
+        return list(a), list(b)
+
     def shuffle_pack(self, nparts, dev_out_ptr, part_offsets):
         arr = (ctypes.c_uint64 * nparts)(*part_offsets)
         self._check(self._L.locust_shuffle_pack(self._h, nparts, dev_out_ptr, arr), "locust_shuffle_pack")
@@ -295,6 +302,9 @@ class WordCount:
         p = ctypes.c_void_p()
         self._check(self._L.locust_exchange_alloc(self._h, nbytes, ctypes.byref(p)), "locust_exchange_alloc")
         return p.value
+
+    def exchange_free(self, dev_ptr):
+        self._check(self._L.locust_exchange_free(self._h, dev_ptr), "locust_exchange_free")
 
     def ipc_export(self, dev_ptr):
         h = ctypes.create_string_buffer(64)

@@ -766,6 +766,19 @@ int locust_exchange_alloc(locust_ctx *c, uint64_t nbytes, void **dev_buf) {
     return LOCUST_OK;
 }
 
+int locust_exchange_free(locust_ctx *c, void *dev_buf) {
+    if (!c || !dev_buf) return LOCUST_E_ARG;
+    CU(cudaSetDevice(c->device));
+    for (size_t i = 0; i < c->exchange_bufs.size(); ++i) {
+        if (c->exchange_bufs[i] != dev_buf) continue;
+        CU(cudaStreamSynchronize(c->stream));
+        CU(cudaFree(dev_buf));
+        c->exchange_bufs.erase(c->exchange_bufs.begin() + (long)i);
+        return LOCUST_OK;
+    }
+    return fail(c, LOCUST_E_ARG, "locust_exchange_free: not a buffer of locust_exchange_alloc on this context");
+}
+
 int locust_ipc_export(locust_ctx *c, const void *dev_buf, uint8_t handle[64]) {
     if (!c || !dev_buf || !handle) return LOCUST_E_ARG;
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");

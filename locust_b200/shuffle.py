@@ -115,17 +115,27 @@ class PeerExchange:
     Rank r owns two buffers of `world` slots each (hash shuffle, gather); slot s of a buffer is
     where rank s writes.  The buffers are cudaMalloc'ed by liblocust, their IPC handles are
     all-gathered once, and every rank maps every other rank's buffers (NVLink peer access).  A
-    slot holds `short_cap` short records plus `long_room` bytes of long records; short_cap is the
-    sender's table size, so short records can never overflow."""
+    slot holds `short_cap` short records plus `long_room` bytes of long records.  By default short_cap
+    is the sender's table size, so short records can never overflow.  With a very large table (BASELINE
+    config 4: 2^27 slots = 4 GB per slot) that is not affordable: `counted` mode starts with small slots,
+    DistributedWordCount counts the records of every part before packing (locust_shuffle_sizes /
+    locust_shuffle_counts, which also lets a full table grow and redo MAP) and the slots are re-made
+    when the largest part of any rank does not fit (ensure_shuffle / ensure_result, collective)."""
 
     HIST_BYTES = 65536 * 8
+    COUNTED_ABOVE = 256 << 20            # slot size from which the slots are sized by counting
 
     def __init__(self, wc, dist, device, table_slots, long_room=16 << 20, group=None, result_room=None, ordered=None,
-                 flag_barrier=True):
+                 flag_barrier=True, counted=None):
         import torch
-        self.wc, self.dist, self.group = wc, dist, group
+        self.wc, self.dist, self.group, self.device = wc, dist, group, device
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self.short_cap = int(table_slots)
+        self.counted = (32 + 32 * self.short_cap + int(long_room) > self.COUNTED_ABOVE) if counted is None else bool(counted)
+        if self.counted:
+            self.short_cap, long_room = min(self.short_cap, 1 << 18), min(int(long_room), 1 << 20)
+        self.long_room = int(long_room)
+        self._need_gather = None
         self.slot_bytes = 32 + 32 * self.short_cap + int(long_room)
         self.slot_bytes = (self.slot_bytes + 31) // 32 * 32
         # ordered jobs: rank 0 owns one slot per rank for that rank's sorted slice (offsets, counts, vals
@@ -141,6 +151,7 @@ class PeerExchange:
             # ordered=True / False: only the buffers that kind of job uses (None: both)
             need_gather = self.rank == 0 and ordered is not True
             need_result = self.rank == 0 and ordered is not False
+            self._need_gather = need_gather
             self.mine = [wc.exchange_alloc(self.slot_bytes * self.world),
                          wc.exchange_alloc(self.slot_bytes * self.world if need_gather else 64),
                          wc.exchange_alloc(self.result_slot * self.world if need_result else 64),
@@ -162,6 +173,50 @@ class PeerExchange:
                 h = allh[r * per:(r + 1) * per]
                 self.bufs.append(tuple(wc.ipc_open(h[64 * i:64 * (i + 1)]) for i in range(nbuf)))
         self._token = torch.zeros(1, dtype=torch.int32, device=device)
+
+    def _remake(self, index, nbytes):
+        """collective: this rank's buffer `index` is replaced by one of nbytes and every rank maps the new ones"""
+        import torch
+        wc = self.wc
+        torch.cuda.synchronize(self.device)
+        self.dist.barrier(group=self.group)                       # nobody is still writing into the old buffers
+        for r, mapped in enumerate(self.bufs):
+            if r != self.rank:
+                wc.ipc_close(mapped[index])
+        wc.exchange_free(self.mine[index])
+        raw = bytes(64)
+        try:
+            self.mine[index] = wc.exchange_alloc(nbytes)
+            raw = wc.ipc_export(self.mine[index])
+        except Exception:                                        # noqa: BLE001 - raised below, on every rank
+            pass
+        handles = torch.tensor(list(raw), dtype=torch.uint8, device=self.device)
+        allh = torch.empty(self.world * 64, dtype=torch.uint8, device=self.device)
+        self.dist.all_gather_into_tensor(allh, handles, group=self.group)
+        allh = bytes(allh.cpu().numpy())
+        if any(allh[r * 64:(r + 1) * 64] == bytes(64) for r in range(self.world)):
+            raise RuntimeError("a rank could not allocate or export a larger exchange buffer")
+        for r in range(self.world):
+            b = list(self.bufs[r])
+            b[index] = self.mine[index] if r == self.rank else wc.ipc_open(allh[r * 64:(r + 1) * 64])
+            self.bufs[r] = tuple(b)
+
+    def ensure_shuffle(self, short_need, long_need):
+        """collective (same arguments on every rank): slots that hold short_need short records and
+        long_need bytes of long records"""
+        if short_need <= self.short_cap and long_need <= self.long_room:
+            return
+        self.short_cap = int(short_need) + int(short_need) // 4 + 1024
+        self.long_room = (int(long_need) + int(long_need) // 4 + 4096 + 31) // 32 * 32
+        self.slot_bytes = 32 + 32 * self.short_cap + self.long_room
+        self._remake(0, self.slot_bytes * self.world)
+
+    def ensure_result(self, slice_need):
+        """collective: result slots on rank 0 that hold a sorted slice of slice_need bytes"""
+        if slice_need <= self.result_slot:
+            return
+        self.result_slot = (int(slice_need) + int(slice_need) // 4 + 4096 + 31) // 32 * 32
+        self._remake(2, self.result_slot * self.world if self.rank == 0 else 64)
 
     def barrier(self):
         """every rank's stream has got this far (its packing kernel has finished, say) before any rank's
@@ -237,6 +292,14 @@ class DistributedWordCount:
         """fused path: part i is written by the packing kernel into rank dests[i]'s buffer
         `which` (0 hash shuffle, 1 gather), slot = my rank; barrier; merge my own slots"""
         px, wc = self.peers, self.b.wc
+        if px.counted:
+            # sizes first (host round trip; a table that overflowed in MAP grows here), largest part of any rank
+            sizes = wc.shuffle_sizes(len(dests))
+            n_short, long_bytes = wc.shuffle_counts(len(dests))
+            t = self.b.sizes_tensor([max(n_short), max(long_bytes)])
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
+            px.ensure_shuffle(*[int(x) for x in t.tolist()])
+            self.last_shuffle_bytes = sum(x for d, x in zip(dests, sizes) if d != self.rank)
         dst = [px.bufs[d][which] + self.rank * px.slot_bytes for d in dests]
         wc.shuffle_pack_peers(dst, px.slot_bytes, px.short_cap)
         px.barrier()
@@ -250,6 +313,10 @@ class DistributedWordCount:
         result buffer; barrier; rank 0 strings the slots together"""
         wc, px = self.b.wc, self.peers
         nbytes = wc.result_part_bytes()
+        if px.counted:
+            t = self.b.sizes_tensor([nbytes])
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
+            px.ensure_result(int(t.item()))
         dst = px.bufs[0][2] + self.rank * px.result_slot
         if nbytes <= px.result_slot:
             wc.result_part_pack(dst)
