@@ -183,6 +183,91 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def c3_on_one_gpu(wc, dev, stream, index, nbytes=2 << 30):
+    """BASELINE config 3's text (1 M vocabulary) on ONE GPU, 2 GiB as at N = 8: the base the N >= 2 numbers compare
+    with (N = 1 of the contract runs config 2, another text).  Timed like the headline, checked against the oracle."""
+    import torch
+    from locust_b200.textgen import TextGen
+    from oracle import parity as par
+    text = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    TextGen.config("C3", total_bytes=16 << 30, device=index).fill_device(text)
+    torch.cuda.synchronize()
+    with torch.cuda.stream(stream):
+        for _ in range(3):
+            wc.run(text)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        maps = []
+        for _ in range(5):
+            wc.run(text)
+            maps.append(wc.stage_ms()[0])
+        e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 5
+    got = wc.result_arrays()
+    ref = par.oracle_arrays(text.cpu().numpy())
+    why = par.same_result(got, ref)
+    return {"workload": "first 2 GiB of the C3 text (1M vocab), one GPU, table 2^%d after growth" % 20, "ms_per_step": ms,
+            "value": nbytes / ms / 1e6, "unit": "GB/s", "map_ms": sum(maps) / len(maps), "unique_keys": int(len(got[2])),
+            "parity": {"oracle": "wc_oracle_fast", "bytes_checked": nbytes, "ok": why is None, "why": why}}
+
+
+def run_driver_c(args):
+    """N GPUs driven from this one process through locust_multi_wordcount_device: the same workload and timing
+    rules as the torchrun arm (device-resident shards, events on rank 0's stream), parity against the oracle."""
+    import threading as th
+    import torch
+    import locust_b200
+    from locust_b200.textgen import TextGen
+    from oracle import parity as par
+    n = args.gpus
+    name, per_gpu, desc = workload(n)
+    if args.mib:
+        per_gpu = args.mib << 20
+        desc += " [size overridden to %d MiB per GPU: NOT the benchmark configuration]" % args.mib
+    total = per_gpu * n
+    ndev = torch.cuda.device_count()
+    devices = list(range(n)) if ndev >= n else [i % ndev for i in range(n)]
+    shards = []
+    for r, d in enumerate(devices):
+        t = torch.empty(per_gpu, dtype=torch.uint8, device="cuda:%d" % d)
+        TextGen.config(name, total_bytes=total, device=d).fill_device(t, byte_offset=r * per_gpu)
+        shards.append(t)
+    for d in set(devices):
+        torch.cuda.synchronize(d)
+    table_log2 = args.table_log2 or (20 if name == "C2" else 22)
+    m = locust_b200.MultiWordCount(devices, table_log2=table_log2)
+    for _ in range(args.warmup):
+        m.run_shards(shards)
+    ms, t0 = [], time.perf_counter()
+    for _ in range(args.steps):
+        wc0 = m.run_shards(shards)
+        ms.append(m.stats()["job_ms"])
+    wall = time.perf_counter() - t0
+    res = wc0.result_arrays()
+    refs = [None] * n
+
+    def orc(r):
+        refs[r] = par.oracle_arrays(shards[r].cpu().numpy())[:3]
+    ts = [th.Thread(target=orc, args=(r,)) for r in range(n)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    parity = dict(par.check_sum_of_shards(refs, res), bytes_checked=total)
+    mean = sum(ms) / len(ms)
+    line = {"metric": METRIC, "value": total / mean / 1e6, "unit": "GB/s", "n_gpus": n, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": mean, "ms_per_step_median": sorted(ms)[len(ms) // 2], "ms_per_step_wall": 1e3 * wall / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "driver": "c (one process, locust_multi_wordcount_device; device time on rank 0's stream from its first kernel to "
+                      "the result in place)",
+            "config": {"workload": desc, "bytes_per_gpu": per_gpu, "devices": devices, "table_log2": table_log2,
+                       "unique_keys": int(len(res[2]))},
+            "shuffle": {"record_bytes_exchanged": m.stats()["record_bytes_exchanged"]}, "parity": parity}
+    print(json.dumps(line), flush=True)
+    m.close()
+    if not parity["ok"]:
+        sys.exit("bench.py --driver c: the result differs from the oracle: %s" % parity.get("why"))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -194,6 +279,13 @@ def main():
                     help="size of the text sample the CPU port is timed on (about 10 s of one core per pass at 256)")
     ap.add_argument("--table-log2", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--other-configs", default="auto", choices=["auto", "none", "all"],
+                    help="after the headline measurement also run BASELINE configs 5 and 4 (8 GiB each, parity-checked) and "
+                         "report them as other_configs; auto = at 8 GPUs")
+    ap.add_argument("--driver", default="torchrun", choices=["torchrun", "c"],
+                    help="N>1: 'torchrun' = one process per GPU (the contract's launch); 'c' = this one process drives all "
+                         "GPUs through locust_multi_* (the C entry point a host program would call)")
+    ap.add_argument("--time-budget", type=float, default=600.0, help="seconds after which optional extras are skipped")
     ap.add_argument("--final", default="ordered", choices=["ordered", "gather"],
                     help="N>1: 'ordered' = parts are key ranges, every rank sorts its range, rank 0 concatenates the "
                          "slices; 'gather' = hash parts, then everything is sent to rank 0 and sorted there")
@@ -207,6 +299,10 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
+    if args.driver == "c":
+        run_driver_c(args)
+        return
+    t_start = time.time()
     if world != args.gpus:
         if world == 1 and args.gpus > 1:
             sys.exit("bench.py --gpus %d must be launched with torch.distributed.run --nproc-per-node %d"
@@ -463,6 +559,25 @@ def main():
         cpu["c1_reference"] = c1_reference(wc)
         input_id = hashlib.sha256(host_np).hexdigest()                 # identity of the generated input
 
+    # ---- extras: the same-text base of the N > 1 series, and the configs the headline does not cover ----
+    c3_single, other = None, None
+    del host, host_np
+    if world == 1 and not args.mib and args.other_configs != "none" and time.time() - t_start < args.time_budget:
+        c3_single = c3_on_one_gpu(wc, dev, stream, local_rank)
+    if world > 1 and (args.other_configs == "all" or (args.other_configs == "auto" and world == 8)):
+        from tools.check_full_configs import run_config
+        del text
+        torch.cuda.empty_cache()
+        other = []
+        for cname in ("C5", "C4"):
+            if time.time() - t_start > args.time_budget:
+                if rank == 0:
+                    other.append({"config": cname, "skipped": "time budget of %.0f s used up" % args.time_budget})
+                continue
+            o = run_config(cname, 1 << 33, world, rank, dev, stream, args.final, args.shuffle)
+            if rank == 0:
+                other.append(o)
+
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps,
@@ -479,13 +594,15 @@ def main():
                            "l2": "input per step (%d MiB per GPU) is larger than the 126 MB L2" % (per_gpu >> 20)},
                 "roofline": roofline, "shuffle": shuffle, "cpu_baseline": cpu, "e2e": e2e, "parity": parity, "clocks": clocks,
                 "gpu_launches": launches_per_step * args.steps, "gpu_launches_per_step": launches_per_step,
-                "stage_ms_last_step": stage_last}
+                "stage_ms_last_step": stage_last, "c3_single_gpu": c3_single, "other_configs": other}
         print(json.dumps(line), flush=True)
     wc.close()
     if world > 1:
         dist.destroy_process_group()
     if rank == 0 and not parity["ok"]:
         sys.exit("bench.py: the timed result differs from the oracle: %s" % parity.get("why", "see stderr"))
+    if rank == 0 and other and any(o.get("parity") and not o["parity"]["ok"] for o in other):
+        sys.exit("bench.py: a result of other_configs differs from the oracle")
 
 
 if __name__ == "__main__":

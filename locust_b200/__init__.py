@@ -48,7 +48,8 @@ class _Config(ctypes.Structure):
 
 
 def lib_path():
-    return os.path.join(_HERE, "liblocust.so")
+    # LOCUST_LIB: development switch, another build of the same library (kernel experiments)
+    return os.environ.get("LOCUST_LIB") or os.path.join(_HERE, "liblocust.so")
 
 
 _lib = None

@@ -58,6 +58,49 @@ LC_HD uint32_t classify16(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
     return (p0 >> 28) | ((p1 >> 24) & 0xF0u) | ((p2 >> 20) & 0xF00u) | ((p3 >> 16) & 0xF000u);
 }
 
+#if defined(__CUDACC__)
+// The same classifier with `nimad` of its nine byte-wise adds issued as multiply-adds (x * one + c, `one` a
+// register holding 1 that the compiler cannot see through): IMAD runs on the FMA pipe, the rest of the
+// classifier on the ALU pipe, and the two pipes issue side by side.
+template <int nimad>
+__device__ __forceinline__ uint32_t classify4_bal(uint32_t x, uint32_t one) {
+    const uint32_t x7 = x & 0x7F7F7F7Fu;
+#define LC_ADD(i, c) ((i) < nimad ? x7 * one + (c) : x7 + (c))
+    const uint32_t r1 = LC_ADD(0, 0x77777777u);
+    const uint32_t r2 = LC_ADD(1, 0x75757575u);
+    const uint32_t r3 = LC_ADD(2, 0x59595959u);
+    const uint32_t r4 = LC_ADD(3, 0x56565656u);
+    const uint32_t r5 = LC_ADD(4, 0x54545454u);
+    const uint32_t r6 = LC_ADD(5, 0x51515151u);
+    const uint32_t r7 = LC_ADD(6, 0x46464646u);
+    const uint32_t r8 = LC_ADD(7, 0x44444444u);
+#undef LC_ADD
+    const uint32_t z = (x7 & 0x7D7D7D7Du) ^ 0x20202020u;
+    const uint32_t nz = (8 < nimad) ? z * one + 0x7F7F7F7Fu : z + 0x7F7F7F7Fu;
+    const uint32_t a = r1 ^ r2 ^ r3;
+    const uint32_t b = r4 ^ r5 ^ r6;
+    const uint32_t c = r7 ^ r8 ^ ~nz;
+    return (a ^ b ^ c) & ~x & 0x80808080u;
+}
+template <int nimad>
+__device__ __forceinline__ uint32_t classify16_bal(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3, uint32_t one) {
+    const uint32_t p0 = classify4_bal<nimad>(w0, one) * 0x00204081u;
+    const uint32_t p1 = classify4_bal<nimad>(w1, one) * 0x00204081u;
+    const uint32_t p2 = classify4_bal<nimad>(w2, one) * 0x00204081u;
+    const uint32_t p3 = classify4_bal<nimad>(w3, one) * 0x00204081u;
+    return (p0 >> 28) | ((p1 >> 24) & 0xF0u) | ((p2 >> 20) & 0xF00u) | ((p3 >> 16) & 0xF000u);
+}
+__device__ __forceinline__ uint32_t opaque_one() { uint32_t v; asm volatile("mov.u32 %0, 1;" : "=r"(v)); return v; }
+// v += (value of v `delta` lanes below), for lanes that have such a lane: the shuffle's own predicate says
+// whether the source lane exists, which saves the compare + select of the intrinsic form
+__device__ __forceinline__ uint32_t scan_step(uint32_t v, uint32_t delta) {
+    asm("{\n\t.reg .pred p;\n\t.reg .u32 t;\n\t"
+        "shfl.sync.up.b32 t|p, %0, %1, 0, 0xffffffff;\n\t"
+        "@p add.u32 %0, %0, t;\n\t}" : "+r"(v) : "r"(delta));
+    return v;
+}
+#endif
+
 LC_HD uint32_t byte_perm(uint32_t a, uint32_t b, uint32_t s) {
 #if defined(__CUDA_ARCH__)
     // raw PRMT: the __byte_perm intrinsic only honours three bits per selector nibble
@@ -137,6 +180,18 @@ LC_HD uint64_t mix64(uint64_t x) {
 }
 LC_HD uint64_t hash_key128(uint64_t k0, uint64_t k1) {
     return mix64(k0 ^ (k1 * 0x9E3779B97F4A7C15ull) ^ (k1 >> 29));
+}
+// Home slot of a key in the global combiner table (at most 2^32 slots): a 32-bit multiply-add over the
+// key's four words and one round of avalanche -- a dozen instructions where the 64-bit mix above costs
+// about forty-five on a GPU without 64-bit integer multipliers.  Every inserter into one table (MAP, the
+// flush of the shared-memory table, the shuffle merge) uses this one function.
+LC_HD uint32_t slot_hash32(uint64_t k0, uint64_t k1) {
+    uint32_t h = (uint32_t)k0 * 0x9E3779B1u + (uint32_t)(k0 >> 32) * 0x85EBCA77u + (uint32_t)k1 * 0xC2B2AE3Du +
+                 (uint32_t)(k1 >> 32) * 0x27D4EB2Fu;
+    h ^= h >> 15; h *= 0x2C1B3C6Du;
+    h ^= h >> 12; h *= 0x297A2D39u;
+    h ^= h >> 15;
+    return h;
 }
 
 // 32 bytes in one access: sm_100 has 256-bit global loads and stores, and the table slots and

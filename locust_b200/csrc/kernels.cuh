@@ -15,6 +15,7 @@ constexpr uint32_t kStatusLongFull  = 2u;   // long-token buffer too small
 constexpr uint32_t kStatusEntryFull = 4u;   // candidate-record buffers too small
 constexpr uint32_t kStatusBlobFull  = 8u;   // key blob too small
 constexpr uint32_t kStatusTextFull  = 16u;  // formatted-text buffer too small
+constexpr uint32_t kStatusFarFull   = 32u;  // list of long-token positions of one MAP launch too small
 
 // One entry of the long-key list: `count` occurrences of the key at ptr[0..len), len > 16.
 // Entries are (all but) distinct keys: long_keys.cuh finds an existing entry through a hash
@@ -35,6 +36,8 @@ struct Counters {
     unsigned long long total;       // sum of counts = tokens
     unsigned long long text_bytes;  // formatted output size
     unsigned long long n_tied;      // records whose 16-byte prefix is shared and that need ordering by their tails
+    unsigned long long n_far;       // long-token occurrences the current MAP launch has listed (can exceed the list)
+    unsigned long long far_peak;    // largest n_far of the job
     uint32_t status;
     uint32_t sort_parity;           // 0: sorted records in buffer A, 1: in buffer B
     uint32_t pass_active[16];       // radix pass p moves data
@@ -79,6 +82,8 @@ struct MapParams {
     uint64_t long_cap;
     uint32_t *long_index;       // open-addressed index over long_list: position + 1, 0 = empty
     uint64_t long_index_mask;   // its slots - 1
+    ulonglong2 *far_list;       // {start, end of input} addresses of tokens longer than 16 bytes met by this launch
+    uint64_t far_cap;
     Counters *ctr;
     uint32_t flags;             // LOCUST_F_*
     Records rec;                // LOCUST_F_SORT_PATH only: every token becomes a record
@@ -114,6 +119,9 @@ int launch_tokenize_combine(const MapParams &p, int num_sms, cudaStream_t st);
 cudaError_t map_stream_setup();
 int launch_tokenize_stream(const MapParams &p, int variant, int num_sms, cudaStream_t st);
 
+// Counts the long tokens a MAP launch has listed (MapParams::far_list) into the long-key list and empties
+// the list for the next launch.  Runs right behind every MAP launch.
+int launch_long_tokens(const MapParams &p, int num_sms, cudaStream_t st);
 // zeroes the long-key index if the counters say the last job used it
 int launch_long_index_clear(const Counters *ctr, uint32_t *index, uint64_t slots, int num_sms, cudaStream_t st);
 

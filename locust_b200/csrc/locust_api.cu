@@ -43,6 +43,8 @@ struct locust_ctx {
     uint64_t slots = 0;
     LongOcc *long_list = nullptr;
     uint64_t long_cap = 0;
+    ulonglong2 *far_list = nullptr;   // positions of long tokens, per MAP launch
+    uint64_t far_cap = 0;
     uint32_t *long_index = nullptr;   // hash index over long_list (long_keys.cuh)
     uint64_t long_index_slots = 0;
     bool long_index_dirty = true;     // freshly allocated: contents undefined
@@ -218,6 +220,8 @@ MapParams map_params(locust_ctx *c, const uint8_t *dev, uint64_t lo_abs, uint64_
     p.table_mask = c->slots - 1;
     p.long_list = c->long_list;
     p.long_cap = c->long_cap;
+    p.far_list = c->far_list;
+    p.far_cap = c->far_cap;
     p.long_index = c->long_index;
     p.long_index_mask = c->long_index_slots - 1;
     p.ctr = c->ctr;
@@ -228,7 +232,9 @@ MapParams map_params(locust_ctx *c, const uint8_t *dev, uint64_t lo_abs, uint64_
 
 int map_device_range(locust_ctx *c, const uint8_t *dev, uint64_t lo, uint64_t hi) {
     if (hi <= lo) return LOCUST_OK;
-    c->launches += (uint64_t)launch_tokenize_combine(map_params(c, dev, lo, hi), c->num_sms, c->stream);
+    const MapParams mp = map_params(c, dev, lo, hi);
+    c->launches += (uint64_t)launch_tokenize_combine(mp, c->num_sms, c->stream);
+    if (mp.flags == 0u) c->launches += (uint64_t)launch_long_tokens(mp, c->num_sms, c->stream);
     CU(cudaGetLastError());
     return LOCUST_OK;
 }
@@ -295,9 +301,20 @@ int run_reduce_async(locust_ctx *c) {
 
 // Grows whatever the status bits name and runs MAP again over the recorded inputs.
 int grow_and_remap(locust_ctx *c, uint32_t st) {
-    if (c->shuffled || !c->replayable)
-        return fail(c, LOCUST_E_CAPACITY, "table too small for the merged records; raise table_log2 / long_capacity");
+    if (c->shuffled || !c->replayable) {
+        static thread_local char msg[160];
+        snprintf(msg, sizeof msg, "table too small for the merged records; raise table_log2 / long_capacity (status bits %u, "
+                                  "%llu long keys of %llu)", st, (unsigned long long)c->h_ctr->n_long, (unsigned long long)c->long_cap);
+        return fail(c, LOCUST_E_CAPACITY, msg);
+    }
     int rc;
+    if (st & kStatusFarFull) {                       // more long tokens in one MAP launch than the position list holds
+        cudaFree(c->far_list); c->far_list = nullptr;
+        uint64_t want = c->h_ctr->far_peak + (c->h_ctr->far_peak >> 3) + 1024;
+        if (want < 2 * c->far_cap) want = 2 * c->far_cap;
+        c->far_cap = want;
+        CU(dalloc(&c->far_list, c->far_cap));
+    }
     if (st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull)) {
         uint64_t slots = c->slots, long_cap = c->long_cap;
         if (st & kStatusTableFull) slots *= 4;
@@ -313,7 +330,7 @@ int grow_and_remap(locust_ctx *c, uint32_t st) {
         if (slots > (1ull << 32)) return fail(c, LOCUST_E_CAPACITY, "combiner table would exceed 2^32 slots");
         rc = alloc_sized(c, slots, long_cap);
         if (rc) return rc;
-    } else {   // only the key blob was too small
+    } else if (st & kStatusBlobFull) {   // the key blob was too small
         cudaFree(c->red.key_blob); c->red.key_blob = nullptr;
         c->red.blob_cap = c->h_ctr->blob_bytes + 64;
         CU(dalloc(&c->red.key_blob, c->red.blob_cap));
@@ -342,11 +359,11 @@ int finish_reduce(locust_ctx *c) {
             return fail(c, LOCUST_E_CAPACITY, "locust_shuffle_pack_peers: records did not fit the destination slot "
                                               "(raise slot_bytes); the job's result is incomplete");
         const uint32_t st = c->h_ctr->status;
-        if (!(st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull | kStatusBlobFull))) {
+        if (!(st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull | kStatusBlobFull | kStatusFarFull))) {
             c->stage = 2;
             return LOCUST_OK;
         }
-        if (c->shuffled && (st & kStatusBlobFull) && !(st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull))) {
+        if (c->shuffled && (st & kStatusBlobFull) && !(st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull | kStatusFarFull))) {
             // merged records stay in the table: only the blob has to grow, then PROCESS + REDUCE again
             cudaFree(c->red.key_blob); c->red.key_blob = nullptr;
             c->red.blob_cap = c->h_ctr->blob_bytes + 64;
@@ -431,6 +448,8 @@ int locust_create(const locust_config *cfg, locust_ctx **out) {
     CU(dalloc(&c->sort.bases, 16 * 256));
     CU(dalloc(&c->sort.tickets, 64));
     CU(cudaMemsetAsync(c->sort.tickets, 0, 64 * sizeof(uint32_t), c->stream));
+    c->far_cap = 1ull << 21;
+    CU(dalloc(&c->far_list, c->far_cap));
     const uint32_t lg = cfg->table_log2 ? cfg->table_log2 : 20;
     const uint64_t long_cap = cfg->long_capacity ? cfg->long_capacity : (1ull << 20);
     int rc = alloc_sized(c, 1ull << lg, long_cap);
@@ -445,7 +464,7 @@ int locust_destroy(locust_ctx *c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     drop_segments(c);
     for (auto &sp : c->spares) cudaFree(sp.ptr);
-    cudaFree(c->table); cudaFree(c->long_list); cudaFree(c->long_index); cudaFree(c->ctr);
+    cudaFree(c->table); cudaFree(c->long_list); cudaFree(c->long_index); cudaFree(c->far_list); cudaFree(c->ctr);
     cudaFree(c->sort.tie_k); cudaFree(c->sort.tie_q);
     free_record_buffers(c);
     cudaFree(c->sort.hist); cudaFree(c->sort.bases); cudaFree(c->sort.tickets);
@@ -721,7 +740,7 @@ int locust_shuffle_sizes(locust_ctx *c, uint32_t nparts, uint64_t *bytes_per_par
         CU(cudaMemcpyAsync(c->h_ctr, c->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
         CU(cudaStreamSynchronize(c->stream));
         const uint32_t st = c->h_ctr->status;
-        if (!(st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull))) break;
+        if (!(st & (kStatusTableFull | kStatusLongFull | kStatusEntryFull | kStatusFarFull))) break;
         if (attempt >= 8) return fail(c, LOCUST_E_CAPACITY, "buffers still too small after repeated growth");
         int rc = grow_and_remap(c, st);
         if (rc) return rc;

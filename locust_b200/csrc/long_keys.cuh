@@ -17,23 +17,68 @@ namespace locust {
 
 constexpr uint32_t kLongBusy = 0xFFFFFFFFu;
 
-LC_D uint64_t long_hash(const uint8_t *s, uint64_t len) {
-    uint64_t h = 0x9E3779B97F4A7C15ull ^ len;
-    for (uint64_t i = 0; i < len; ++i) h = (h ^ s[i]) * 0x100000001B3ull;
-    h = mix64(h);
+// The MAP kernels keep almost all of the SM's L1 as shared memory, so a byte-at-a-time walk over a token
+// costs one L2 round trip per byte.  Long keys are therefore read eight bytes at a time: chunk k of a key is
+// its bytes [8k, 8k + 8), put together from the one or two aligned 64-bit words that hold them (aligned words
+// never straddle a page, and a word is only touched if it holds a byte of the key), zero padded past the end.
+LC_D uint64_t long_chunk(const uint8_t *key, uint64_t k, uint64_t len) {
+    const uint64_t a = reinterpret_cast<uint64_t>(key) + 8ull * k, rem = len - 8ull * k;      // rem > 0
+    const uint64_t *w = reinterpret_cast<const uint64_t *>(a & ~7ull);
+    const uint32_t off = (uint32_t)(a & 7ull), sh = 8u * off;
+    uint64_t c = __ldcg(w) >> sh;
+    if (off != 0u && rem > 8ull - off) c |= __ldcg(w + 1) << (64u - sh);
+    if (rem < 8ull) c &= (1ull << (8u * (uint32_t)rem)) - 1ull;
+    return c;
+}
+LC_D uint64_t long_mix(uint64_t h, uint64_t chunk) {
+    h = (h ^ chunk) * 0x9E3779B97F4A7C15ull;
+    return h ^ (h >> 32);
+}
+LC_D uint64_t long_finish(uint64_t h, uint64_t len) {
+    h = mix64(h ^ (len * 0xD6E8FEB86659FD93ull));
     return h ? h : 1ull;
+}
+constexpr uint64_t kLongSeed = 0x243F6A8885A308D3ull;
+
+LC_D uint64_t long_hash(const uint8_t *s, uint64_t len) {
+    uint64_t h = kLongSeed;
+    for (uint64_t k = 0; 8ull * k < len; ++k) h = long_mix(h, long_chunk(s, k, len));
+    return long_finish(h, len);
 }
 
 LC_D bool long_equal(const uint8_t *a, const uint8_t *b, uint64_t len) {
     if (a == b) return true;
-    for (uint64_t i = 0; i < len; ++i)
-        if (a[i] != b[i]) return false;
+    for (uint64_t k = 0; 8ull * k < len; ++k)
+        if (long_chunk(a, k, len) != long_chunk(b, k, len)) return false;
     return true;
 }
 
-// Adds `inc` occurrences of the key s[0..len) (len > 16) to the long-key list.  `s` must stay valid
+// Length and hash of the token that starts at s in one pass: at most maxlen bytes belong to the input (the
+// token ends at the first delimiter or there).  Eight bytes at a time, delimiters found with the SWAR classifier.
+LC_D uint64_t long_scan(const uint8_t *s, uint64_t maxlen, uint64_t &hash) {
+    uint64_t h = kLongSeed, L = 0;
+    for (uint64_t k = 0; 8ull * k < maxlen; ++k) {
+        uint64_t c = long_chunk(s, k, maxlen);
+        const uint64_t rem = maxlen - 8ull * k;
+        if (rem < 8ull) c |= 0x0A0A0A0A0A0A0A0Aull << (8u * (uint32_t)rem);           // beyond the input: a delimiter
+        const uint32_t f0 = classify4((uint32_t)c), f1 = classify4((uint32_t)(c >> 32));
+        if (f0 | f1) {
+            const uint32_t nb = f0 ? ((uint32_t)__ffs((int)f0) - 1u) >> 3 : 4u + (((uint32_t)__ffs((int)f1) - 1u) >> 3);
+            if (nb) h = long_mix(h, c & ((1ull << (8u * nb)) - 1ull));
+            L += nb;
+            hash = long_finish(h, L);
+            return L;
+        }
+        h = long_mix(h, c);
+        L += 8ull;
+    }
+    hash = long_finish(h, L);
+    return L;
+}
+
+// Adds `inc` occurrences of the key s[0..len) (len > 16, h = its long_hash) to the long-key list.  `s` must stay valid
 // until the job's result has been produced (it points into the input, or into a received part).
-LC_D void long_insert(const MapParams &p, const uint8_t *s, uint64_t len, unsigned long long inc) {
+__device__ __noinline__ static void long_insert(const MapParams &p, const uint8_t *s, uint64_t len, uint64_t h, unsigned long long inc) {
     if (p.long_cap == 0) {                           // no room at all (locust_count_static): reported, not stored
         atomicAdd(&p.ctr->n_long, 1ull);
         atomicOr(&p.ctr->status, kStatusLongFull);
@@ -41,11 +86,12 @@ LC_D void long_insert(const MapParams &p, const uint8_t *s, uint64_t len, unsign
     }
     // a list that is already known to be too small: the host grows it and redoes the job
     if (*reinterpret_cast<volatile uint32_t *>(&p.ctr->status) & kStatusLongFull) return;
-    const uint64_t h = long_hash(s, len);
     uint64_t slot = h & p.long_index_mask;
     for (uint64_t probe = 0; probe <= p.long_index_mask; ++probe, slot = (slot + 1) & p.long_index_mask) {
-        uint32_t v;
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p.long_index + slot) : "memory");
+        // read through L2 (other SMs write these words), without an acquire: that would invalidate this SM's L1
+        // on every long token.  The entry's fields are read through L2 too, at an address that depends on the
+        // value read here, and the writer fences between writing the entry and publishing its position.
+        uint32_t v = __ldcg(p.long_index + slot);
         if (v == 0u) {
             v = atomicCAS(p.long_index + slot, 0u, kLongBusy);
             if (v == 0u) {                           // ours: make the entry, then publish its position
@@ -56,18 +102,36 @@ LC_D void long_insert(const MapParams &p, const uint8_t *s, uint64_t len, unsign
                 }
                 LongOcc *e = p.long_list + idx;
                 e->ptr = s; e->len = len; e->count = inc; e->hash = h;
-                asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.long_index + slot), "r"((uint32_t)idx + 1u) : "memory");
+                __threadfence();
+                __stcg(p.long_index + slot, (uint32_t)idx + 1u);
                 return;
             }
         }
         if (v == kLongBusy) continue;                // being written: cannot compare, move on
-        const LongOcc *e = p.long_list + (v - 1u);
-        if (e->hash == h && e->len == len && long_equal(e->ptr, s, len)) {
+        const ulonglong2 pl = __ldcg(reinterpret_cast<const ulonglong2 *>(p.long_list + (v - 1u)));          // ptr, len
+        const uint64_t eh = __ldcg(&p.long_list[v - 1u].hash);
+        if (eh == h && pl.y == len && long_equal(reinterpret_cast<const uint8_t *>(pl.x), s, len)) {
             atomicAdd(&p.long_list[v - 1u].count, inc);
             return;
         }
     }
     atomicOr(&p.ctr->status, kStatusLongFull);
+}
+
+// MAP's fast kernels do not walk long tokens themselves (that needs registers and an L1 they do not have):
+// they list where each one starts, and long_tokens_kernel (process_kernels.cu) takes it from there.
+LC_D void far_push(const MapParams &p, uint64_t pos) {
+    const unsigned long long idx = atomicAdd(&p.ctr->n_far, 1ull);
+    if (idx < p.far_cap) p.far_list[idx] = make_ulonglong2(reinterpret_cast<unsigned long long>(p.base + pos), reinterpret_cast<unsigned long long>(p.base + p.hi));
+    else atomicOr(&p.ctr->status, kStatusFarFull);
+}
+
+// The token that starts at s is longer than 16 bytes: find its end, hash it, count it.  Out of line: the MAP
+// kernels call it from their rare path and must not pay its registers in their main loop.
+__device__ __noinline__ static void long_token_at(const MapParams &p, const uint8_t *s, uint64_t maxlen) {
+    uint64_t h;
+    const uint64_t L = long_scan(s, maxlen, h);
+    long_insert(p, s, L, h, 1ull);
 }
 
 }  // namespace locust

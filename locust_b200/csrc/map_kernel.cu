@@ -39,6 +39,16 @@ static_assert(kSmemBytes <= 232448, "shared memory budget of one CTA");
 static_assert(kWarpArea % 16 == 0 && kQueueOff % 16 == 0, "alignment");
 constexpr uint32_t kFull = 0xFFFFFFFFu;
 constexpr uint32_t kMaxProbe = 1u << 14;
+#ifndef LOCUST_IMAD
+#define LOCUST_IMAD 4
+#endif
+#ifndef LOCUST_SCANSTEP
+#define LOCUST_SCANSTEP 1
+#endif
+#ifndef LOCUST_SLOT32
+#define LOCUST_SLOT32 1
+#endif
+constexpr int kImadAdds = LOCUST_IMAD;                     // of the classifier's nine adds per word, issued on the FMA pipe
 constexpr uint32_t kSegments = 1;                 // pieces of the input per warp (8 measured: -2.5% on C2, +4% on C5)
 
 LC_D uint4 ldg_stream(const uint8_t *p) {
@@ -65,7 +75,11 @@ LC_D void cas128(Slot *s, uint64_t n0, uint64_t n1, uint64_t &o0, uint64_t &o1) 
 // kPlain: the job runs with flags == 0, so no test switch has to be looked at.
 template <bool kPlain>
 __device__ __noinline__ void global_insert(const MapParams &p, uint64_t k0, uint64_t k1, unsigned long long inc) {
+#if LOCUST_SLOT32
+    uint64_t h = slot_hash32(k0, k1);
+#else
     uint64_t h = hash_key128(k0, k1);
+#endif
     if (!kPlain && (p.flags & LOCUST_F_WEAK_HASH)) h &= 0xFFull;
     uint64_t slot = h & p.table_mask;
     for (uint32_t probe = 0; probe < kMaxProbe; ++probe) {
@@ -88,6 +102,7 @@ struct WarpCtx {
     uint32_t area;         // byte offset of this warp's area
     uint32_t qn;           // entries queued (warp-uniform)
     uint32_t lane;
+    uint32_t sb;           // shared address of smem_raw
     bool use_smem;
 };
 #define WC_SKEYS reinterpret_cast<ulonglong2 *>(smem_raw)
@@ -104,7 +119,15 @@ LC_D uint32_t smem_bucket(uint32_t lo, uint32_t hi) {
 }
 // Fast probe used per token: counts the token if its key already sits in the bucket, without
 // a divergent branch.  A miss is queued by the caller; the queue's drain claims free ways.
-LC_D bool smem_hit(const WarpCtx &wc, uint32_t lo, uint32_t hi) {
+// Branch free, on 32-bit shared addresses (wc.sb = the CTA's shared window, kept in a register: the
+// generic-pointer form recomputed it from a special register for every batch): a predicated 128-bit load of
+// the bucket, two compares, two predicated atomics.  `probe` says whether this lane has a key of <= 8 bytes.
+#ifndef LOCUST_ASM_PROBE
+#define LOCUST_ASM_PROBE 1
+#endif
+#if !LOCUST_ASM_PROBE
+LC_D bool smem_hit(const WarpCtx &wc, uint32_t lo, uint32_t hi, bool probe) {
+    if (!probe) return false;
     const uint32_t b = smem_bucket(lo, hi);
     const uint4 kb = reinterpret_cast<const uint4 *>(WC_SKEYS)[b];
     const uint32_t d0 = (kb.x ^ lo) | (kb.y ^ hi), d1 = (kb.z ^ lo) | (kb.w ^ hi);
@@ -112,6 +135,34 @@ LC_D bool smem_hit(const WarpCtx &wc, uint32_t lo, uint32_t hi) {
     if (hit) atomicAdd(&WC_SCNT[2 * b + (d1 == 0u ? 1u : 0u)], 1u);
     return hit;
 }
+#else
+LC_D bool smem_hit(const WarpCtx &wc, uint32_t lo, uint32_t hi, bool probe) {
+    uint32_t hit;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred ps, p0, p1;\n\t"
+        ".reg .u32 h, ad, k0, k1, k2, k3, x0, x1;\n\t"
+        "setp.ne.u32 ps, %4, 0;\n\t"
+        "mul.lo.u32 h, %1, 0x9E3779B1;\n\t"
+        "mad.lo.u32 h, %2, 0x85EBCA77, h;\n\t"
+        "mul.hi.u32 h, h, %5;\n\t"
+        "mad.lo.u32 ad, h, 16, %3;\n\t"
+        "mov.u32 k0, 0;\n\tmov.u32 k1, 0;\n\tmov.u32 k2, 0;\n\tmov.u32 k3, 0;\n\t"
+        "@ps ld.shared.v4.u32 {k0, k1, k2, k3}, [ad];\n\t"
+        "xor.b32 x0, k0, %1;\n\txor.b32 x1, k1, %2;\n\tor.b32 x0, x0, x1;\n\t"
+        "setp.eq.and.u32 p0, x0, 0, ps;\n\t"
+        "xor.b32 x0, k2, %1;\n\txor.b32 x1, k3, %2;\n\tor.b32 x0, x0, x1;\n\t"
+        "setp.eq.and.u32 p1, x0, 0, ps;\n\t"
+        "mad.lo.u32 ad, h, 8, %3;\n\t"
+        "@p0 red.shared.add.u32 [ad+%6], 1;\n\t"
+        "@p1 red.shared.add.u32 [ad+%7], 1;\n\t"
+        "or.pred p0, p0, p1;\n\t"
+        "selp.u32 %0, 1, 0, p0;\n\t"
+        "}"
+        : "=r"(hit) : "r"(lo), "r"(hi), "r"(wc.sb), "r"((uint32_t)probe), "n"(kBuckets), "n"(kKeysBytes), "n"(kKeysBytes + 4) : "memory");
+    return hit != 0u;
+}
+#endif
 // Full insert: counts `inc` occurrences, claiming a free way if the key is not there yet.  False
 // if the bucket is taken by two other keys (or a claim was lost): the key goes to the global table.
 LC_D bool smem_insert(const WarpCtx &wc, uint32_t lo, uint32_t hi, uint32_t inc) {
@@ -143,9 +194,7 @@ __device__ __noinline__ void token_generic(const MapParams &p, const WarpCtx &wc
         ++L;
     }
     if (L == 16 && L < maxlen && !is_delim(s[16])) {
-        L = 17;
-        while (L < maxlen && !is_delim(s[L])) ++L;
-        long_insert(p, s, L, 1ull);
+        long_token_at(p, s, maxlen);
         return;
     }
     if (L <= 8 && (kPlain || wc.use_smem)) {
@@ -252,8 +301,8 @@ LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active
         }
         return;
     }
-    bool defer = has;
-    if (has && L <= 8u && (kPlain || wc.use_smem)) defer = !smem_hit(wc, a, b);
+    const bool hit = smem_hit(wc, a, b, has && L <= 8u && (kPlain || wc.use_smem));
+    const bool defer = has && !hit;
     const uint32_t m = __ballot_sync(kFull, defer);
     if (m) {
         if (defer)
@@ -263,7 +312,10 @@ LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active
         if (wc.qn >= 32u) drain_queue<kPlain>(p, wc, 32u);
     }
     if (__any_sync(kFull, far)) {
-        if (far) token_generic<kPlain>(p, wc, ROW_POS() + pos);
+        if (far) {
+            if (kPlain) far_push(p, ROW_POS() + pos);                 // walked by long_tokens_kernel behind this launch
+            else token_generic<kPlain>(p, wc, ROW_POS() + pos);
+        }
         __syncwarp();
     }
 #undef ROW_POS
@@ -292,6 +344,9 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
     wc.qn = 0u;
     wc.lane = lane;
     wc.use_smem = kPlain || !(p.flags & LOCUST_F_NO_SMEM_COMBINER);
+    wc.sb = (uint32_t)__cvta_generic_to_shared(smem_raw);
+    asm volatile("mov.u32 %0, %0;" : "+r"(wc.sb));            // kept in a register
+    const uint32_t one = opaque_one();
     uint16_t *bits16 = reinterpret_cast<uint16_t *>(WC_BITS(wc));
 
     for (uint32_t seg = 0; seg < kSegments; ++seg) {
@@ -318,8 +373,8 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
         };
         uint4 c = load_row(0u);
         uint4 n = load_row(1u);
-        uint32_t dc = classify16(c.x, c.y, c.z, c.w);
-        uint32_t dn = classify16(n.x, n.y, n.z, n.w);
+        uint32_t dc = classify16_bal<kImadAdds>(c.x, c.y, c.z, c.w, one);
+        uint32_t dn = classify16_bal<kImadAdds>(n.x, n.y, n.z, n.w, one);
         bool asc_c = !__any_sync(kFull, (c.x | c.y | c.z | c.w) & 0x80808080u);
         bool asc_n = !__any_sync(kFull, (n.x | n.y | n.z | n.w) & 0x80808080u);
         // mask of the chunk in front of lane 0; only its top bit (last byte) is used
@@ -342,11 +397,16 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
                 // dense list of token starts: warp prefix sum of the per-lane counts
                 const uint32_t cnt = __popc(starts);
                 uint32_t incl = cnt;
+#if LOCUST_SCANSTEP
+                incl = scan_step(incl, 1); incl = scan_step(incl, 2); incl = scan_step(incl, 4);
+                incl = scan_step(incl, 8); incl = scan_step(incl, 16);
+#else
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
                     const uint32_t y = __shfl_up_sync(kFull, incl, o);
                     if (lane >= (uint32_t)o) incl += y;
                 }
+#endif
                 const uint32_t total = __shfl_sync(kFull, incl, 31);
                 uint32_t at = incl;                                         // filled from the back: order within a row is free
                 while (starts) {
@@ -370,7 +430,7 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
             }
             pd = dc; c = n; dc = dn; asc_c = asc_n;
             n = nn;
-            dn = classify16(n.x, n.y, n.z, n.w);
+            dn = classify16_bal<kImadAdds>(n.x, n.y, n.z, n.w, one);
             asc_n = !__any_sync(kFull, (n.x | n.y | n.z | n.w) & 0x80808080u);
         }
     }
@@ -392,7 +452,11 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
         for (uint32_t j = 0; j < kFlush; ++j) {
             const uint32_t i = base + j * kMapThreads;
             k[j] = i < kSmemSlots ? keys[i] : 0ull;
+#if LOCUST_SLOT32
+            uint64_t h = slot_hash32(k[j], 0ull);
+#else
             uint64_t h = hash_key128(k[j], 0ull);
+#endif
             if (!kPlain && (p.flags & LOCUST_F_WEAK_HASH)) h &= 0xFFull;
             home[j] = p.table + (h & p.table_mask);
             cur[j] = make_ulonglong2(0ull, 0ull);
@@ -439,7 +503,7 @@ __global__ void __launch_bounds__(256) shuffle_merge_kernel(const uint8_t *__res
         while (done < long_bytes) {
             const unsigned long long len = reinterpret_cast<const unsigned long long *>(q + done)[0];
             const unsigned long long cnt = reinterpret_cast<const unsigned long long *>(q + done)[1];
-            long_insert(p, q + done + 16, len, cnt);             // the same key from several senders becomes one entry
+            long_insert(p, q + done + 16, len, long_hash(q + done + 16, len), cnt);             // the same key from several senders becomes one entry
             done += 16ull + ((len + 15ull) & ~15ull);
         }
     }

@@ -131,15 +131,6 @@ LC_D uint32_t prmt(uint32_t a, uint32_t b, uint32_t s) {
     asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(s));
     return r;
 }
-// v += (value of v `delta` lanes below), for lanes that have such a lane: the shuffle's own predicate
-// says whether the source lane exists, which saves the compare + select of the intrinsic form
-LC_D uint32_t scan_step(uint32_t v, uint32_t delta) {
-    asm("{\n\t.reg .pred p;\n\t.reg .u32 t;\n\t"
-        "shfl.sync.up.b32 t|p, %0, %1, 0, 0xffffffff;\n\t"
-        "@p add.u32 %0, %0, t;\n\t}" : "+r"(v) : "r"(delta));
-    return v;
-}
-
 LC_D void cas128(Slot *s, uint64_t n0, uint64_t n1, uint64_t &o0, uint64_t &o1) {
     asm volatile(
         "{\n\t"
@@ -150,38 +141,6 @@ LC_D void cas128(Slot *s, uint64_t n0, uint64_t n1, uint64_t &o0, uint64_t &o1) 
         "mov.b128 {%0, %1}, d;\n\t"
         "}\n"
         : "=l"(o0), "=l"(o1) : "l"(s), "l"(0ull), "l"(n0), "l"(n1) : "memory");
-}
-
-// SWAR classifier of common.cuh with `nimad` of its nine byte-wise adds issued as multiply-adds
-// (x * one + c, `one` a register the compiler cannot see through): IMAD runs on the FMA pipe, the
-// rest of the classifier on the ALU pipe, and the two pipes issue side by side.
-template <int nimad>
-LC_D uint32_t classify4_bal(uint32_t x, uint32_t one) {
-    const uint32_t x7 = x & 0x7F7F7F7Fu;
-#define LC_ADD(i, c) ((i) < nimad ? x7 * one + (c) : x7 + (c))
-    const uint32_t r1 = LC_ADD(0, 0x77777777u);   // >= 09
-    const uint32_t r2 = LC_ADD(1, 0x75757575u);   // >= 0B
-    const uint32_t r3 = LC_ADD(2, 0x59595959u);   // >= 27
-    const uint32_t r4 = LC_ADD(3, 0x56565656u);   // >= 2A
-    const uint32_t r5 = LC_ADD(4, 0x54545454u);   // >= 2C
-    const uint32_t r6 = LC_ADD(5, 0x51515151u);   // >= 2F
-    const uint32_t r7 = LC_ADD(6, 0x46464646u);   // >= 3A
-    const uint32_t r8 = LC_ADD(7, 0x44444444u);   // >= 3C
-#undef LC_ADD
-    const uint32_t z = (x7 & 0x7D7D7D7Du) ^ 0x20202020u;
-    const uint32_t nz = (8 < nimad) ? z * one + 0x7F7F7F7Fu : z + 0x7F7F7F7Fu;   // top bit iff z != 0
-    const uint32_t a = r1 ^ r2 ^ r3;
-    const uint32_t b = r4 ^ r5 ^ r6;
-    const uint32_t c = r7 ^ r8 ^ ~nz;
-    return (a ^ b ^ c) & ~x & 0x80808080u;
-}
-template <int nimad>
-LC_D uint32_t classify16_bal(uint4 v, uint32_t one) {
-    const uint32_t p0 = classify4_bal<nimad>(v.x, one) * 0x00204081u;
-    const uint32_t p1 = classify4_bal<nimad>(v.y, one) * 0x00204081u;
-    const uint32_t p2 = classify4_bal<nimad>(v.z, one) * 0x00204081u;
-    const uint32_t p3 = classify4_bal<nimad>(v.w, one) * 0x00204081u;
-    return (p0 >> 28) | ((p1 >> 24) & 0xF0u) | ((p2 >> 20) & 0xF00u) | ((p3 >> 16) & 0xF000u);
 }
 
 // ---- the CTA's combiner table (keys of <= 8 bytes): buckets of two 64-bit keys side by side ----
@@ -247,7 +206,7 @@ LC_D void insert_batches(const MapParams &p, const Table<kTok> &tab, const ulong
         inc[j] = !same ? 1u : (lane == leader ? (uint32_t)__popc(agg) : 0u);
         if ((k[j].x | k[j].y) == 0ull) inc[j] = 0u;
         if (inc[j] && k[j].y == 0ull && tab.insert((uint32_t)k[j].x, (uint32_t)(k[j].x >> 32), inc[j])) inc[j] = 0u;
-        home[j] = p.table + (hash_key128(k[j].x, k[j].y) & p.table_mask);
+        home[j] = p.table + ((uint64_t)slot_hash32(k[j].x, k[j].y) & p.table_mask);
         cur[j] = make_ulonglong2(0ull, 0ull);
         if (inc[j]) cur[j] = __ldcg(reinterpret_cast<const ulonglong2 *>(home[j]));
     }
@@ -262,24 +221,6 @@ LC_D void insert_batches(const MapParams &p, const Table<kTok> &tab, const ulong
         if (o0 == k[j].x && o1 == k[j].y) atomicAdd(&home[j]->count, (unsigned long long)inc[j]);
         else global_probe(p, (uint64_t)((home[j] - p.table) + 1) & p.table_mask, k[j].x, k[j].y, (unsigned long long)inc[j]);
     }
-}
-
-// Token longer than 16 bytes (or whose end lies beyond the 32-bit delimiter window) starting at
-// base[pos]: counted in the long-key list (long_keys.cuh), found there by hash and full compare.
-__device__ __noinline__ void long_token(const MapParams &p, uint64_t pos) {
-    const uint8_t *s = p.base + pos;
-    const uint64_t maxlen = p.hi - pos;
-    uint64_t L = 0;
-    while (L < maxlen && !is_delim(s[L])) ++L;
-    if (L <= 16) {                                  // cannot happen on this path; kept so that no token is ever lost
-        uint64_t k0 = 0, k1 = 0;
-        for (uint64_t i = 0; i < L; ++i) {
-            if (i < 8) k0 |= (uint64_t)s[i] << (8 * i); else k1 |= (uint64_t)s[i] << (8 * (i - 8));
-        }
-        if (L) global_probe(p, hash_key128(k0, k1) & p.table_mask, k0, k1, 1ull);
-        return;
-    }
-    long_insert(p, s, L, 1ull);
 }
 
 // 16 bytes at byte offset `off` from base that straddle lo or hi: bytes outside [lo, hi) read as '\n'
@@ -412,7 +353,7 @@ __global__ void __launch_bounds__((kTok + kIns) * 32, 1) tokenize_stream_kernel(
                     c1 = mask_chunk(p, b0 + 512u + lane * 16u, c1);
                 }
                 asc_n = !__any_sync(kFull, (c0.x | c0.y | c0.z | c0.w | c1.x | c1.y | c1.z | c1.w) & 0x80808080u);
-                return classify16_bal<kImad>(c0, one) | (classify16_bal<kImad>(c1, one) << 16);
+                return classify16_bal<kImad>(c0.x, c0.y, c0.z, c0.w, one) | (classify16_bal<kImad>(c1.x, c1.y, c1.z, c1.w, one) << 16);
             };
             fetch(0); fetch(1);
             uint32_t dc = classify_row(0);
@@ -538,8 +479,8 @@ __global__ void __launch_bounds__((kTok + kIns) * 32, 1) tokenize_stream_kernel(
                         qn += n0 + (uint32_t)__popc(m1);
                         if (qn >= 32u) hand_over();
                         if (__any_sync(kFull, (e0 | e1) >= 0x4400u)) {
-                            if (e0 >= 0x4400u) long_token(p, row_pos + (e0 & 0x3FFu));
-                            if (e1 >= 0x4400u) long_token(p, row_pos + (e1 & 0x3FFu));
+                            if (e0 >= 0x4400u) far_push(p, row_pos + (e0 & 0x3FFu));
+                            if (e1 >= 0x4400u) far_push(p, row_pos + (e1 & 0x3FFu));
                             __syncwarp();
                         }
                     }
@@ -552,7 +493,7 @@ __global__ void __launch_bounds__((kTok + kIns) * 32, 1) tokenize_stream_kernel(
                         qn += (uint32_t)__popc(m0);
                         if (qn >= 32u) hand_over();
                         if (__any_sync(kFull, e0 >= 0x4400u)) {
-                            if (e0 >= 0x4400u) long_token(p, row_pos + (e0 & 0x3FFu));
+                            if (e0 >= 0x4400u) far_push(p, row_pos + (e0 & 0x3FFu));
                             __syncwarp();
                         }
                     }
@@ -614,7 +555,7 @@ __global__ void __launch_bounds__((kTok + kIns) * 32, 1) tokenize_stream_kernel(
         for (uint32_t j = 0; j < kFlush; ++j) {
             const uint32_t i = base + j * kThreads;
             k[j] = i < L::kSlots ? lds64(tab.keys + 8u * i) : 0ull;
-            home[j] = p.table + (hash_key128(k[j], 0ull) & p.table_mask);
+            home[j] = p.table + ((uint64_t)slot_hash32(k[j], 0ull) & p.table_mask);
             cur[j] = make_ulonglong2(0ull, 0ull);
             if (k[j]) cur[j] = __ldcg(reinterpret_cast<const ulonglong2 *>(home[j]));
         }

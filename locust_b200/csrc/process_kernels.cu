@@ -8,6 +8,7 @@
 // longer than 16 bytes are put in order afterwards by full comparison inside
 // their run of equal prefixes.
 #include "kernels.cuh"
+#include "long_keys.cuh"
 #include "lookback.cuh"
 
 namespace locust {
@@ -423,6 +424,27 @@ __global__ void __launch_bounds__(256) tie_fix_kernel(Records r, const Counters 
     }
 }
 
+// One thread per listed long token: end and hash in one word-wise pass, then the long-key list.  This kernel
+// has the registers and the L1 the MAP kernels lack (they keep the SM's L1 as shared memory).  A token the list
+// says is long may turn out to have <= 16 bytes only if the caller listed it wrongly; it is counted all the same.
+__global__ void __launch_bounds__(256) long_tokens_kernel(const __grid_constant__ MapParams p) {
+    unsigned long long n = p.ctr->n_far;
+    if (n == 0ull) return;
+    if (n > p.far_cap) n = p.far_cap;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const ulonglong2 e = p.far_list[i];
+        const uint8_t *s = reinterpret_cast<const uint8_t *>(e.x);
+        uint64_t h;
+        const uint64_t L = long_scan(s, e.y - e.x, h);
+        long_insert(p, s, L, h, 1ull);
+    }
+}
+__global__ void far_reset_kernel(Counters *ctr) {
+    if (ctr->n_far > ctr->far_peak) ctr->far_peak = ctr->n_far;
+    ctr->n_far = 0ull;
+}
+
 __global__ void __launch_bounds__(256) long_index_clear_kernel(const Counters *ctr, uint32_t *index, uint64_t slots) {
     if (ctr->n_long == 0ull) return;
     uint4 *z = reinterpret_cast<uint4 *>(index);
@@ -437,6 +459,12 @@ static inline unsigned grid_for(uint64_t n, unsigned per_block, int num_sms, int
     if (g > cap) g = cap;
     if (g < 1) g = 1;
     return (unsigned)g;
+}
+
+int launch_long_tokens(const MapParams &p, int num_sms, cudaStream_t st) {
+    long_tokens_kernel<<<num_sms * 4, 256, 0, st>>>(p);
+    far_reset_kernel<<<1, 1, 0, st>>>(p.ctr);
+    return 2;
 }
 
 int launch_long_index_clear(const Counters *ctr, uint32_t *index, uint64_t slots, int num_sms, cudaStream_t st) {

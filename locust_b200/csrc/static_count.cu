@@ -129,7 +129,7 @@ extern "C" int locust_count_static(const void *dev_data, uint64_t nbytes, void *
     e = cudaMemcpyAsync(&h, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) { say(errbuf, errlen, "reading the counters back", e); return LOCUST_E_CUDA; }
-    if (h.status & kStatusLongFull) {
+    if (h.status & (kStatusLongFull | kStatusFarFull)) {
         say(errbuf, errlen, "locust_count_static: the input holds a word longer than 16 bytes; use locust_create/locust_map");
         return LOCUST_E_CAPACITY;
     }

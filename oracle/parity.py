@@ -123,6 +123,40 @@ def _checksum(rows, counts, base):
         return int(np.bitwise_xor.reduce(h ^ (h >> np.uint64(32)))) & 0x7FFFFFFFFFFFFFFF
 
 
+def check_sum_of_shards(shard_oracles, global_result):
+    """One process holds everything: the global (blob, offsets, counts, vals) equals the key-wise sum of the
+    per-shard oracle results, is strictly ascending, and vals are the prefix sums.  Returns a dict."""
+    W = 2
+    for s in shard_oracles:
+        if len(s[2]):
+            W = max(W, (int(np.diff(np.asarray(s[1]).astype(np.int64)).max()) + 7) // 8)
+    if len(global_result[2]):
+        W = max(W, (int(np.diff(np.asarray(global_result[1]).astype(np.int64)).max()) + 7) // 8)
+    rows = np.concatenate([packed(s[0], s[1], W) for s in shard_oracles], axis=0)
+    counts = np.concatenate([np.asarray(s[2]).astype(np.uint64) for s in shard_oracles])
+    want_rows, want_counts = sum_by_key(rows, counts)
+    g_rows = packed(global_result[0], global_result[1], W)
+    g_counts = np.asarray(global_result[2]).astype(np.uint64)
+    res = {"oracle": "wc_oracle_fast on every shard, records added up by key", "keys": int(len(g_counts)), "ok": True}
+    if len(want_counts) != len(g_counts):
+        res.update(ok=False, why="unique keys: got %d, oracle %d" % (len(g_counts), len(want_counts)))
+    elif len(g_counts) and not np.array_equal(want_rows, g_rows):
+        res.update(ok=False, why="keys differ from the oracle's")
+    elif len(g_counts) and not np.array_equal(want_counts, g_counts):
+        i = int(np.flatnonzero(want_counts != g_counts)[0])
+        res.update(ok=False, why="count of key %d is %d, oracle %d" % (i, int(g_counts[i]), int(want_counts[i])))
+    elif not _strictly_ascending(g_rows):
+        res.update(ok=False, why="keys are not strictly ascending")
+    else:
+        vals = np.asarray(global_result[3]).astype(np.uint64)
+        want_vals = np.concatenate([[0], np.cumsum(g_counts)[:-1]]).astype(np.uint64) if len(g_counts) else vals
+        if not np.array_equal(vals, want_vals):
+            res.update(ok=False, why="vals are not the exclusive prefix sums of counts")
+    if res["ok"]:
+        res["tokens"] = int(g_counts.sum())
+    return res
+
+
 def check_distributed(dist, device, rank, world, shard_oracle, my_slice, global_result):
     """Exact parity of a multi-rank ordered job, run on every rank:
 
