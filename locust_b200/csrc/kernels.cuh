@@ -16,6 +16,8 @@ constexpr uint32_t kStatusEntryFull = 4u;   // candidate-record buffers too smal
 constexpr uint32_t kStatusBlobFull  = 8u;   // key blob too small
 constexpr uint32_t kStatusTextFull  = 16u;  // formatted-text buffer too small
 constexpr uint32_t kStatusFarFull   = 32u;  // list of long-token positions of one MAP launch too small
+constexpr uint32_t kStatusBadPart   = 64u;  // a received part does not have the layout of a packed part
+constexpr uint32_t kStatusTieFull   = 128u; // more records with a shared 16-byte prefix than the tie arrays hold
 
 // One entry of the long-key list: `count` occurrences of the key at ptr[0..len), len > 16.
 // Entries are (all but) distinct keys: long_keys.cuh finds an existing entry through a hash

@@ -7,9 +7,9 @@
 // matched by hash, length and a full byte compare against the bytes the list entry points at, so
 // every further occurrence only adds to the entry's count.
 //
-// Claiming is two-step (slot -> kBusy, entry written, slot -> position) without waiting: a thread
-// that meets a slot in the busy state cannot compare, so it moves on and may create a second entry
-// for the same key.  That is rare and harmless: REDUCE adds up records with equal keys.
+// Claiming is two-step (slot -> kBusy, entry written, slot -> position).  A thread that meets a slot in the
+// busy state waits a bounded moment for the position; if it still cannot compare it moves on and may
+// create a second entry for the same key.  That is rare and harmless: REDUCE adds up records with equal keys.
 #pragma once
 #include "kernels.cuh"
 
@@ -25,8 +25,8 @@ LC_D uint64_t long_chunk(const uint8_t *key, uint64_t k, uint64_t len) {
     const uint64_t a = reinterpret_cast<uint64_t>(key) + 8ull * k, rem = len - 8ull * k;      // rem > 0
     const uint64_t *w = reinterpret_cast<const uint64_t *>(a & ~7ull);
     const uint32_t off = (uint32_t)(a & 7ull), sh = 8u * off;
-    uint64_t c = __ldcg(w) >> sh;
-    if (off != 0u && rem > 8ull - off) c |= __ldcg(w + 1) << (64u - sh);
+    uint64_t c = *w >> sh;                              // input text: read-only for the whole job
+    if (off != 0u && rem > 8ull - off) c |= w[1] << (64u - sh);
     if (rem < 8ull) c &= (1ull << (8u * (uint32_t)rem)) - 1ull;
     return c;
 }
@@ -107,7 +107,11 @@ __device__ __noinline__ static void long_insert(const MapParams &p, const uint8_
                 return;
             }
         }
-        if (v == kLongBusy) continue;                // being written: cannot compare, move on
+        for (int spin = 0; v == kLongBusy && spin < 256; ++spin) {          // being written by its claimer: a moment
+            __nanosleep(32);
+            v = __ldcg(p.long_index + slot);
+        }
+        if (v == kLongBusy) continue;                // still not published: cannot compare, move on (a duplicate entry at worst)
         const ulonglong2 pl = __ldcg(reinterpret_cast<const ulonglong2 *>(p.long_list + (v - 1u)));          // ptr, len
         const uint64_t eh = __ldcg(&p.long_list[v - 1u].hash);
         if (eh == h && pl.y == len && long_equal(reinterpret_cast<const uint8_t *>(pl.x), s, len)) {

@@ -488,7 +488,7 @@ __global__ void __launch_bounds__(256) shuffle_merge_kernel(const uint8_t *__res
     const unsigned long long *hdr = reinterpret_cast<const unsigned long long *>(part);
     const unsigned long long n_short = hdr[0], long_bytes = hdr[1], long_off = hdr[2];
     if (32ull + 32ull * n_short > long_off || long_off + long_bytes > nbytes) {     // malformed part: refuse loudly
-        if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(&p.ctr->status, kStatusEntryFull);
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(&p.ctr->status, kStatusEntryFull | kStatusBadPart);
         return;
     }
     const ulonglong4 *rec = reinterpret_cast<const ulonglong4 *>(part + 32);

@@ -319,6 +319,8 @@ LC_D int cmp_full(const Records &r, const Rec *recs, uint32_t a, uint32_t b) {
     return cmp_tail(r, x, y);
 }
 
+constexpr uint32_t kTieLocal = 2048;
+
 LC_D void grid_meet(uint32_t *bar, uint32_t &generation) {
     ++generation;
     __syncthreads();
@@ -364,7 +366,7 @@ __global__ void __launch_bounds__(256) tie_sort_kernel(Records r, SortScratch sc
             if (tied) {
                 const unsigned long long at = base + __popc(m & ((1u << lane) - 1u));
                 if (at < sc.tie_cap) { K[at] = (uint32_t)i; Q[at] = (uint32_t)i; }
-                else atomicOr(&ctr->status, kStatusEntryFull);
+                else atomicOr(&ctr->status, kStatusEntryFull | kStatusTieFull);
             }
         }
     }
@@ -374,6 +376,33 @@ __global__ void __launch_bounds__(256) tie_sort_kernel(Records r, SortScratch sc
     if (m < 2ull || m > sc.tie_cap) return;
     uint64_t M = 2;
     while (M < m) M <<= 1;
+    if (M <= kTieLocal) {
+        // a handful of ties (the usual case: two spellings of one long word, duplicates of a racing insert): one
+        // block sorts them in shared memory, no grid barriers
+        if (blockIdx.x != 0) return;
+        __shared__ uint32_t sk[kTieLocal], sq[kTieLocal];
+        for (uint32_t j = threadIdx.x; j < (uint32_t)M; j += blockDim.x) { sk[j] = j < m ? K[j] : 0xFFFFFFFFu; sq[j] = sk[j]; }
+        __syncthreads();
+        for (uint32_t k = 2; k <= (uint32_t)M; k <<= 1) {
+            for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+                for (uint32_t i = threadIdx.x; i < (uint32_t)M; i += blockDim.x) {
+                    const uint32_t l = i ^ j;
+                    if (l <= i) continue;
+                    const bool asc = (i & k) == 0;
+                    const uint32_t ka = sk[i], kb = sk[l];
+                    if ((cmp_full(r, recs, ka, kb) > 0) == asc) { sk[i] = kb; sk[l] = ka; }
+                    const uint32_t qa = sq[i], qb = sq[l];
+                    if ((qa > qb) == asc) { sq[i] = qb; sq[l] = qa; }
+                }
+                __syncthreads();
+            }
+        }
+        for (uint32_t j = threadIdx.x; j < (uint32_t)m; j += blockDim.x) st256(spare + j, ld256(recs + sk[j]));
+        __syncthreads();
+        __threadfence_block();
+        for (uint32_t j = threadIdx.x; j < (uint32_t)m; j += blockDim.x) st256(recs + sq[j], ld256(spare + j));
+        return;
+    }
     for (uint64_t j = m + tid; j < M; j += nthreads) { K[j] = 0xFFFFFFFFu; Q[j] = 0xFFFFFFFFu; }
     grid_meet(bar, generation);
     // 2. bitonic sort of K (by key) and Q (by position)
@@ -431,13 +460,30 @@ __global__ void __launch_bounds__(256) long_tokens_kernel(const __grid_constant_
     unsigned long long n = p.ctr->n_far;
     if (n == 0ull) return;
     if (n > p.far_cap) n = p.far_cap;
-    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
-         i += (unsigned long long)gridDim.x * blockDim.x) {
-        const ulonglong2 e = p.far_list[i];
-        const uint8_t *s = reinterpret_cast<const uint8_t *>(e.x);
-        uint64_t h;
-        const uint64_t L = long_scan(s, e.y - e.x, h);
-        long_insert(p, s, L, h, 1ull);
+    const uint32_t lane = threadIdx.x & 31u;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long i0 = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x - lane; i0 < n; i0 += stride) {
+        const unsigned long long i = i0 + lane;
+        const bool valid = i < n;
+        const uint8_t *s = nullptr;
+        uint64_t h = 0, L = 0;
+        if (valid) {
+            const ulonglong2 e = p.far_list[i];
+            s = reinterpret_cast<const uint8_t *>(e.x);
+            L = long_scan(s, e.y - e.x, h);
+        }
+        // equal keys of the warp are added up first: a frequent long word would otherwise put every one of its
+        // occurrences on the same counter in L2
+        const uint32_t peers = __match_any_sync(kFull, valid ? h : 0ull);
+        const uint32_t leader = (uint32_t)__ffs((int)peers) - 1u;
+        const unsigned long long ls = __shfl_sync(kFull, reinterpret_cast<unsigned long long>(s), leader);
+        const unsigned long long ll = __shfl_sync(kFull, (unsigned long long)L, leader);
+        const bool same = valid && ll == L && long_equal(reinterpret_cast<const uint8_t *>(ls), s, L);
+        const uint32_t agg = __ballot_sync(kFull, same) & peers;
+        if (valid) {
+            if (!same) long_insert(p, s, L, h, 1ull);
+            else if (lane == leader) long_insert(p, s, L, h, (unsigned long long)__popc(agg));
+        }
     }
 }
 __global__ void far_reset_kernel(Counters *ctr) {
@@ -462,7 +508,7 @@ static inline unsigned grid_for(uint64_t n, unsigned per_block, int num_sms, int
 }
 
 int launch_long_tokens(const MapParams &p, int num_sms, cudaStream_t st) {
-    long_tokens_kernel<<<num_sms * 4, 256, 0, st>>>(p);
+    long_tokens_kernel<<<num_sms * 8, 256, 0, st>>>(p);
     far_reset_kernel<<<1, 1, 0, st>>>(p.ctr);
     return 2;
 }

@@ -14,6 +14,13 @@ pytestmark = pytest.mark.gpu
 torch = pytest.importorskip("torch")
 
 
+def dev_zeros(*a, **k):
+    """zeroed CUDA tensor, finished: the contexts enqueue on their own streams, not on torch's"""
+    t = torch.zeros(*a, **k)
+    torch.cuda.synchronize()
+    return t
+
+
 @pytest.fixture(scope="module")
 def lb():
     if not torch.cuda.is_available():
@@ -41,11 +48,12 @@ def emulate(lb, data, P, **kw):
             for x in sizes:
                 offs.append(acc)
                 acc += x
-            buf = torch.zeros(acc, dtype=torch.uint8, device="cuda")
+            buf = dev_zeros(acc, dtype=torch.uint8, device="cuda")
             ctx[s].shuffle_pack(nparts, buf.data_ptr(), offs)
             keep.append(buf)
             for i, (o, x) in enumerate(zip(offs, sizes)):
                 inbox[dest_of_part[i]].append((buf, o, x))
+        torch.cuda.synchronize()                         # every part packed before anybody merges (the ranks' barrier)
         for r in range(P):
             ctx[r].shuffle_begin_merge()
             for buf, o, x in inbox[r]:
@@ -91,7 +99,7 @@ def test_hash_partitions_are_disjoint_and_balanced(lb):
     wc.reset()
     wc.map(dev)
     sizes = wc.shuffle_sizes(P)
-    buf = torch.zeros(sum(sizes), dtype=torch.uint8, device="cuda")
+    buf = dev_zeros(sum(sizes), dtype=torch.uint8, device="cuda")
     offs = [sum(sizes[:i]) for i in range(P)]
     wc.shuffle_pack(P, buf.data_ptr(), offs)
     torch.cuda.synchronize()
@@ -204,9 +212,9 @@ def emulate_ordered(lb, data, P, via="concat", room=None, hist_via="shared", **k
     ctx = [lb.WordCount(device=0, **kw) for _ in range(P)]
     keep = []
     try:
-        hist = torch.zeros(lb.PARTITION_BINS, dtype=torch.int64, device="cuda")
-        slots = torch.zeros(P * lb.PARTITION_BINS, dtype=torch.int64, device="cuda")
-        own = [torch.zeros(lb.PARTITION_BINS, dtype=torch.int64, device="cuda") for _ in range(P)]
+        hist = dev_zeros(lb.PARTITION_BINS, dtype=torch.int64, device="cuda")
+        slots = dev_zeros(P * lb.PARTITION_BINS, dtype=torch.int64, device="cuda")
+        own = [dev_zeros(lb.PARTITION_BINS, dtype=torch.int64, device="cuda") for _ in range(P)]
         torch.cuda.synchronize()
         for r, (lo, hi) in enumerate(shards):
             ctx[r].reset()
@@ -227,13 +235,14 @@ def emulate_ordered(lb, data, P, via="concat", room=None, hist_via="shared", **k
         for s in range(P):
             sizes = ctx[s].shuffle_sizes(P)
             offs = [sum(sizes[:i]) for i in range(P)]
-            buf = torch.zeros(sum(sizes), dtype=torch.uint8, device="cuda")
+            buf = dev_zeros(sum(sizes), dtype=torch.uint8, device="cuda")
             torch.cuda.synchronize()
             ctx[s].shuffle_pack(P, buf.data_ptr(), offs)
             keep.append(buf)
             for i in range(P):
                 inbox[i].append((buf, offs[i], sizes[i]))
         slices, parts = [], []
+        torch.cuda.synchronize()                         # every part packed before anybody merges (the ranks' barrier)
         for r in range(P):
             ctx[r].shuffle_begin_merge()
             for buf, o, x in inbox[r]:
@@ -242,7 +251,7 @@ def emulate_ordered(lb, data, P, via="concat", room=None, hist_via="shared", **k
             ctx[r].reduce()
             k, c, _ = ctx[r].result()
             slices.append((k, c))
-            part = torch.zeros(ctx[r].result_part_bytes(), dtype=torch.uint8, device="cuda")
+            part = dev_zeros(ctx[r].result_part_bytes(), dtype=torch.uint8, device="cuda")
             torch.cuda.synchronize()
             ctx[r].result_part_pack(part.data_ptr())
             parts.append(part)
@@ -252,7 +261,7 @@ def emulate_ordered(lb, data, P, via="concat", room=None, hist_via="shared", **k
         if via == "slots":
             # what ranks on one box do: every slice packed into its slot of one buffer, strung together from there
             slot = room if room is not None else (max(p.numel() for p in parts) + 64) // 32 * 32
-            landing = torch.zeros(slot * P, dtype=torch.uint8, device="cuda")
+            landing = dev_zeros(slot * P, dtype=torch.uint8, device="cuda")
             torch.cuda.synchronize()
             for r in range(P):
                 if parts[r].numel() <= slot:
@@ -337,9 +346,9 @@ def test_peer_barrier_alone_and_put_to_many(lb):
     the two-rank case runs on real GPUs in bench.py --gpus 2 and tools/check_peer_exchange.py"""
     c = lb.WordCount(device=0, table_log2=10)
     try:
-        flags = torch.zeros(64, dtype=torch.int32, device="cuda")
+        flags = dev_zeros(64, dtype=torch.int32, device="cuda")
         src = torch.arange(4096, dtype=torch.int32, device="cuda")
-        dst = torch.zeros(3, 4096, dtype=torch.int32, device="cuda")
+        dst = dev_zeros(3, 4096, dtype=torch.int32, device="cuda")
         torch.cuda.synchronize()
         c.reset()
         c.map(torch.frombuffer(bytearray(b"a b"), dtype=torch.uint8).cuda())
@@ -362,7 +371,7 @@ def test_range_parts_need_matching_nparts(lb):
         d = torch.frombuffer(bytearray(b"a b c d"), dtype=torch.uint8).cuda()
         c.reset()
         c.map(d)
-        hist = torch.zeros(lb.PARTITION_BINS, dtype=torch.int64, device="cuda")
+        hist = dev_zeros(lb.PARTITION_BINS, dtype=torch.int64, device="cuda")
         torch.cuda.synchronize()
         c.partition_histogram(hist.data_ptr())
         c.partition_by_range(hist.data_ptr(), 4)
