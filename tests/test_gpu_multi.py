@@ -87,3 +87,17 @@ def test_cli_on_several_ranks(lb, tmp_path):
     keep = lambda out: [l for l in out.split(b"\n") if l.startswith(b"print key: ")]
     assert keep(many) == keep(one) and len(keep(one)) == 5608
     assert b"".join(l + b"\n" for l in keep(many)) == golden_ref_cpu("hamlet")
+
+
+def test_peer_exchange_under_torchrun(lb):
+    """the real thing: one process per GPU, IPC-mapped peer buffers, flag barriers across processes, every
+    exchange path against the oracle (tools/check_peer_exchange.py).  Needs two GPUs; the one-GPU box skips."""
+    import sys
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("one GPU: the ranks of this path are separate processes on separate GPUs")
+    n = 2 if n < 4 else 4
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(n), "--master-addr", "127.0.0.1",
+                        "--master-port", "29733", os.path.join(ROOT, "tools", "check_peer_exchange.py")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert r.stdout.count("keys match the oracle") >= 10 and r.stdout.count("ok") >= n

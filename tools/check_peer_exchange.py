@@ -26,14 +26,18 @@ results = {}
 with torch.cuda.stream(st):
     px = PeerExchange(wc, dist, dev, 1 << log2)
     px_nccl_barrier = PeerExchange(wc, dist, dev, 1 << log2, flag_barrier=False)
+    px_counted = PeerExchange(wc, dist, dev, 1 << log2, counted=True)        # slots sized from a count pass, grown on demand
     for name, peers, ordered in (("gather nccl", None, False), ("gather peers", px, False), ("gather peers again", px, False),
                                  ("ordered nccl", None, True), ("ordered peers", px, True), ("ordered peers again", px, True),
-                                 ("ordered peers, all-reduce barrier", px_nccl_barrier, True)):
+                                 ("ordered peers, all-reduce barrier", px_nccl_barrier, True),
+                                 ("ordered peers, counted slots", px_counted, True), ("ordered peers, counted slots again", px_counted, True),
+                                 ("gather peers, counted slots", px_counted, False)):
         job = DistributedWordCount(GpuBackend(wc, dev), dist, peers=peers, ordered=ordered)
         job.run(text)
         results[name] = (wc.result()[:2], ordered)
     px.close()
     px_nccl_barrier.close()
+    px_counted.close()
 gathered = [None] * world
 dist.all_gather_object(gathered, bytes(text.cpu().numpy()))
 if rank == 0:
