@@ -21,20 +21,37 @@
 
 #include "kernels.cuh"
 #include "long_keys.cuh"
+#include "smem_ptx.cuh"
 #include "../../include/locust.h"
 
 namespace locust {
 
 constexpr int kMapThreads = 1024;
 constexpr int kMapWarps = kMapThreads / 32;
-constexpr uint32_t kBuckets = (232448u - (kMapThreads / 32) * 2160u) / 24u / 8u * 8u;               // shared table: buckets of two 64-bit keys
+#ifndef LOCUST_INS
+#define LOCUST_INS 0
+#endif
+// EXPERIMENT, off by default (LOCUST_INS = 0): of the 32 warps, kInsWarps only insert.  The tokenising warps hand
+// them their queued keys through a ring in shared memory (kXSlots batches of 32 keys, an mbarrier pair per slot), so
+// that the L2 round trips of the global table stall warps that have nothing else to do.  Correct on inputs up to
+// 256 MiB, but at 1 GiB a build with two inserting warps stopped making progress (not understood; the same hand-over
+// in map_stream_kernel.cu passes at 1 GiB), so the shipped kernel tokenises with all 32 warps.
+constexpr int kInsWarps = LOCUST_INS;
+constexpr uint32_t kXSlots = 8;
+constexpr uint32_t oXHead = 0, oXTail = 4, oXDone = 8, oXFull = 16, oXEmpty = oXFull + 8 * kXSlots, oXCount = oXEmpty + 8 * kXSlots, oXData = 256;
+constexpr uint32_t kXBytes = oXData + kXSlots * 512;
+constexpr uint32_t kPoison = 0xFFFFFFFFu;
+constexpr uint32_t kBuckets = (232448u - kXBytes - (kMapThreads / 32) * 2160u) / 24u / 16u * 16u;       // shared table: buckets of two 64-bit keys
 constexpr uint32_t kSmemSlots = 2 * kBuckets;
 constexpr uint32_t kQueueSlots = 64;              // per warp, 16 bytes each
 // per-warp area: staged row (512 + 32), delimiter bits (17 words, padded), token list, queue
 constexpr uint32_t kRowOff = 0, kBitsOff = 544, kDescOff = 624, kQueueOff = 1136;
 constexpr uint32_t kWarpArea = kQueueOff + kQueueSlots * 16;           // 2160
 constexpr uint32_t kKeysBytes = kBuckets * 16, kCntBytes = kSmemSlots * 4;
-constexpr uint32_t kSmemBytes = kKeysBytes + kCntBytes + kMapWarps * kWarpArea;
+constexpr uint32_t kXOff = kKeysBytes + kCntBytes;                      // hand-over ring
+constexpr uint32_t kAreasOff = kXOff + kXBytes;
+constexpr uint32_t kSmemBytes = kAreasOff + kMapWarps * kWarpArea;
+static_assert(kXOff % 128 == 0, "alignment of the hand-over ring");
 static_assert(kSmemBytes <= 232448, "shared memory budget of one CTA");
 static_assert(kWarpArea % 16 == 0 && kQueueOff % 16 == 0, "alignment");
 constexpr uint32_t kFull = 0xFFFFFFFFu;
@@ -258,6 +275,99 @@ LC_D void drain_queue(const MapParams &p, WarpCtx &wc, uint32_t keep_below) {
     }
 }
 
+// kDepth batches of 32 queued keys at once (key j of this lane in k[j], zero = none), for the inserting warps:
+// the same steps as drain_queue, but the home slots of everything bound for the global table are read together,
+// so that the L2 round trips of up to kDepth batches overlap.
+template <int kDepth>
+LC_D void insert_keys(const MapParams &p, const WarpCtx &wc, const ulonglong2 (&k)[kDepth]) {
+    uint32_t inc[kDepth];
+    Slot *home[kDepth];
+    ulonglong2 cur[kDepth];
+#pragma unroll
+    for (int j = 0; j < kDepth; ++j) {
+        const uint32_t h = (uint32_t)k[j].x * 0x9E3779B1u + (uint32_t)(k[j].x >> 32) * 0x85EBCA77u +
+                           (uint32_t)k[j].y * 0xC2B2AE3Du + (uint32_t)(k[j].y >> 32) * 0x27D4EB2Fu;
+        const uint32_t peers = __match_any_sync(kFull, h);
+        const uint32_t leader = (uint32_t)__ffs((int)peers) - 1u;
+        const unsigned long long lx = __shfl_sync(kFull, k[j].x, leader), ly = __shfl_sync(kFull, k[j].y, leader);
+        const bool same = k[j].x == lx && k[j].y == ly;
+        const uint32_t agg = __ballot_sync(kFull, same) & peers;
+        inc[j] = !same ? 1u : (wc.lane == leader ? (uint32_t)__popc(agg) : 0u);
+        if ((k[j].x | k[j].y) == 0ull) inc[j] = 0u;
+        if (inc[j] && k[j].y == 0ull && smem_insert(wc, (uint32_t)k[j].x, (uint32_t)(k[j].x >> 32), inc[j])) inc[j] = 0u;
+        home[j] = p.table + ((uint64_t)slot_hash32(k[j].x, k[j].y) & p.table_mask);
+        cur[j] = make_ulonglong2(0ull, 0ull);
+        if (inc[j]) cur[j] = __ldcg(reinterpret_cast<const ulonglong2 *>(home[j]));
+    }
+#pragma unroll
+    for (int j = 0; j < kDepth; ++j) {
+        if (!inc[j]) continue;
+        uint64_t o0 = cur[j].x, o1 = cur[j].y;
+        if ((o0 | o1) == 0ull) {
+            cas128(home[j], k[j].x, k[j].y, o0, o1);
+            if ((o0 | o1) == 0ull) { o0 = k[j].x; o1 = k[j].y; }
+        }
+        if (o0 == k[j].x && o1 == k[j].y) atomicAdd(&home[j]->count, (unsigned long long)inc[j]);
+        else global_insert<true>(p, k[j].x, k[j].y, (unsigned long long)inc[j]);
+    }
+}
+
+// The top 32 queued keys of a tokenising warp go to an inserting warp; when the ring is full the warp inserts
+// them itself.  A place in the ring is taken by compare-and-swap on the head while fewer than kXSlots batches are
+// outstanding (the barriers' phase parity cannot tell use k of a slot from use k + 2).
+LC_D void hand_over(const MapParams &p, WarpCtx &wc) {
+    const uint32_t xb = wc.sb + kXOff;
+    while (wc.qn >= 32u) {
+        __syncwarp();
+        uint32_t idx = 0, got = 0;
+        if (wc.lane == 0) {
+            idx = lds32(xb + oXHead);
+            const uint32_t tail = lds32(xb + oXTail);
+            if (idx - tail < kXSlots) got = atoms_cas32(xb + oXHead, idx, idx + 1u) == idx ? 1u : 0u;
+        }
+        got = __shfl_sync(kFull, got, 0);
+        idx = __shfl_sync(kFull, idx, 0);
+        if (!got) { drain_queue<true>(p, wc, wc.qn - 31u); continue; }          // one batch, here
+        const uint32_t s = idx % kXSlots, round = idx / kXSlots;
+        mbar_wait(xb + oXEmpty + 8 * s, (round & 1u) ^ 1u);
+        const uint4 kk = lds128(wc.sb + wc.area + kQueueOff + 16u * (wc.qn - 32u + wc.lane));
+        sts128(xb + oXData + s * 512u + wc.lane * 16u, kk.x, kk.y, kk.z, kk.w);
+        if (wc.lane == 0) sts32(xb + oXCount + 4 * s, 32u);
+        __syncwarp();
+        if (wc.lane == 0) mbar_arrive(xb + oXFull + 8 * s);
+        wc.qn -= 32u;
+    }
+}
+
+// An inserting warp: batches idx = w, w + kInsWarps, ... in order, up to four that are ready at a time.
+LC_D void inserter_loop(const MapParams &p, const WarpCtx &wc, uint32_t w) {
+    const uint32_t xb = wc.sb + kXOff;
+#ifndef LOCUST_INS_DEPTH
+#define LOCUST_INS_DEPTH 4
+#endif
+    constexpr int kDepth = LOCUST_INS_DEPTH;
+    bool stop = false;
+    for (uint32_t idx = w; !stop;) {
+        ulonglong2 k[kDepth];
+        uint32_t taken = 0;
+#pragma unroll
+        for (int j = 0; j < kDepth; ++j) {
+            k[j] = make_ulonglong2(0ull, 0ull);
+            if (stop || (j > 0 && taken != (uint32_t)j)) continue;              // batches are taken in order, without gaps
+            const uint32_t s = idx % kXSlots, round = idx / kXSlots;
+            if (j == 0) mbar_wait(xb + oXFull + 8 * s, round & 1u);
+            else if (!__shfl_sync(kFull, (uint32_t)mbar_test(xb + oXFull + 8 * s, round & 1u), 0)) continue;   // not handed over yet: next time
+            if (lds32(xb + oXCount + 4 * s) == kPoison) { stop = true; continue; }
+            k[j] = lds128q(xb + oXData + s * 512u + wc.lane * 16u);
+            __syncwarp();
+            if (wc.lane == 0) { mbar_arrive(xb + oXEmpty + 8 * s); atoms_add(xb + oXTail, 1u); }
+            idx += (uint32_t)kInsWarps;
+            ++taken;
+        }
+        if (taken) insert_keys<kDepth>(p, wc, k);
+    }
+}
+
 // Phase B for one batch: lane `wc.lane` takes token number t of the row (if active).
 // All lanes call this together.
 template <bool kPlain>
@@ -309,7 +419,10 @@ LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active
             WC_QUEUE(wc)[wc.qn + __popc(m & ((1u << wc.lane) - 1u))] =
                 make_ulonglong2((uint64_t)a | ((uint64_t)b << 32), (uint64_t)c | ((uint64_t)d << 32));
         wc.qn += __popc(m);
-        if (wc.qn >= 32u) drain_queue<kPlain>(p, wc, 32u);
+        if (wc.qn >= 32u) {
+            if (kPlain && kInsWarps > 0) hand_over(p, wc);
+            else drain_queue<kPlain>(p, wc, 32u);
+        }
     }
     if (__any_sync(kFull, far)) {
         if (far) {
@@ -325,13 +438,23 @@ template <bool kPlain>
 __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const __grid_constant__ MapParams p) {
     {
         uint4 *z = reinterpret_cast<uint4 *>(smem_raw);
-        for (uint32_t i = threadIdx.x; i < (kKeysBytes + kCntBytes) / 16; i += kMapThreads) z[i] = make_uint4(0, 0, 0, 0);
+        for (uint32_t i = threadIdx.x; i < (kKeysBytes + kCntBytes + oXData) / 16; i += kMapThreads) z[i] = make_uint4(0, 0, 0, 0);
     }
     __syncthreads();
+    constexpr bool kSplit = kPlain && kInsWarps > 0;
+    constexpr uint32_t kTokWarps = kSplit ? kMapWarps - kInsWarps : kMapWarps;
+    if (kSplit) {
+        if (threadIdx.x == 0) {
+            const uint32_t xb = (uint32_t)__cvta_generic_to_shared(smem_raw) + kXOff;
+            for (uint32_t s = 0; s < kXSlots; ++s) { mbar_init(xb + oXFull + 8 * s, 1); mbar_init(xb + oXEmpty + 8 * s, 1); }
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+    }
 
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint64_t nwarps = (uint64_t)gridDim.x * kMapWarps;
-    const uint64_t gw = (uint64_t)blockIdx.x * kMapWarps + warp;
+    const uint64_t nwarps = (uint64_t)gridDim.x * kTokWarps;
+    const uint64_t gw = (uint64_t)blockIdx.x * kTokWarps + warp;
     // rows of 512 bytes counted from base; only rows that overlap [lo, hi) are handed out
     const uint64_t row_lo = p.lo >> 9, nrows = ((p.hi + 511ull) >> 9) - row_lo;
     // Every warp gets kSegments contiguous pieces spread evenly over the input instead of one:
@@ -340,7 +463,7 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
     const uint64_t seg_len = (nrows + nwarps * kSegments - 1) / (nwarps * kSegments);
     const bool use_fast = kPlain || !(p.flags & LOCUST_F_GENERIC_TOKENISER);
     WarpCtx wc;
-    wc.area = kKeysBytes + kCntBytes + warp * kWarpArea;
+    wc.area = kAreasOff + warp * kWarpArea;
     wc.qn = 0u;
     wc.lane = lane;
     wc.use_smem = kPlain || !(p.flags & LOCUST_F_NO_SMEM_COMBINER);
@@ -348,6 +471,9 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
     asm volatile("mov.u32 %0, %0;" : "+r"(wc.sb));            // kept in a register
     const uint32_t one = opaque_one();
     uint16_t *bits16 = reinterpret_cast<uint16_t *>(WC_BITS(wc));
+    if (kSplit && warp >= kTokWarps) {
+        inserter_loop(p, wc, warp - kTokWarps);
+    } else {
 
     for (uint32_t seg = 0; seg < kSegments; ++seg) {
         const uint64_t r0 = row_lo + (seg * nwarps + gw) * seg_len;
@@ -435,6 +561,25 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
         }
     }
     drain_queue<kPlain>(p, wc, 1u);
+    if (kSplit) {
+        // the last tokenising warp to finish tells every inserting warp to stop
+        const uint32_t xb = wc.sb + kXOff;
+        uint32_t d = 0;
+        if (lane == 0) d = atoms_add_ret(xb + oXDone, 1u);
+        d = __shfl_sync(kFull, d, 0);
+        if (d == kTokWarps - 1u) {
+            for (int j = 0; j < kInsWarps; ++j) {
+                uint32_t idx = 0;
+                if (lane == 0) idx = atoms_add_ret(xb + oXHead, 1u);
+                idx = __shfl_sync(kFull, idx, 0);
+                const uint32_t s = idx % kXSlots, round = idx / kXSlots;
+                mbar_wait(xb + oXEmpty + 8 * s, (round & 1u) ^ 1u);
+                if (lane == 0) { sts32(xb + oXCount + 4 * s, kPoison); mbar_arrive(xb + oXFull + 8 * s); }
+                __syncwarp();
+            }
+        }
+    }
+    }   // tokenising warp
     __syncthreads();
     // Flush the CTA's combiner into the global table.  All 148 CTAs arrive here at about the same
     // time with mostly the same keys, and a thread has a dozen slots to flush: done one after the
@@ -539,7 +684,8 @@ int launch_tokenize_combine(const MapParams &p, int num_sms, cudaStream_t st) {
     if (p.hi <= p.lo) return 0;
     if (p.flags == 0u && map_variant() >= 0) return launch_tokenize_stream(p, map_variant(), num_sms, st);
     const uint64_t nrows = ((p.hi + 511ull) >> 9) - (p.lo >> 9);
-    uint64_t ctas = (nrows + kMapWarps - 1) / kMapWarps;
+    const uint64_t per_cta = p.flags == 0u ? (uint64_t)(kMapWarps - kInsWarps) : (uint64_t)kMapWarps;
+    uint64_t ctas = (nrows + per_cta - 1) / per_cta;
     if (ctas > (uint64_t)num_sms) ctas = (uint64_t)num_sms;
     if (p.flags == 0u) tokenize_combine_kernel<true><<<(unsigned)ctas, kMapThreads, kSmemBytes, st>>>(p);
     else tokenize_combine_kernel<false><<<(unsigned)ctas, kMapThreads, kSmemBytes, st>>>(p);

@@ -33,6 +33,7 @@
 
 #include "kernels.cuh"
 #include "long_keys.cuh"
+#include "smem_ptx.cuh"
 #include "../../include/locust.h"
 
 namespace locust {
@@ -68,69 +69,6 @@ struct Layout {
     static_assert(kBytes <= kSmemBudget, "shared memory budget of one CTA");
 };
 
-// ---- shared-memory and barrier primitives on 32-bit shared addresses --------------------------
-LC_D uint32_t lds16(uint32_t a) { uint32_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
-LC_D uint32_t lds32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
-LC_D uint4 lds128(uint32_t a) {
-    uint4 v;
-    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
-    return v;
-}
-LC_D ulonglong2 lds128q(uint32_t a) {
-    ulonglong2 v;
-    asm volatile("ld.shared.v2.u64 {%0,%1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"(a));
-    return v;
-}
-LC_D unsigned long long lds64(uint32_t a) { unsigned long long v; asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(a)); return v; }
-LC_D void sts16(uint32_t a, uint32_t v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
-LC_D void sts32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
-LC_D void sts128(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
-    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
-}
-LC_D void atoms_add(uint32_t a, uint32_t v) { asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
-LC_D uint32_t atoms_add_ret(uint32_t a, uint32_t v) {
-    uint32_t r;
-    asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(r) : "r"(a), "r"(v) : "memory");
-    return r;
-}
-LC_D uint32_t atoms_cas32(uint32_t a, uint32_t cmp, uint32_t val) {
-    uint32_t r;
-    asm volatile("atom.shared.cas.b32 %0, [%1], %2, %3;" : "=r"(r) : "r"(a), "r"(cmp), "r"(val) : "memory");
-    return r;
-}
-LC_D unsigned long long atoms_cas64(uint32_t a, unsigned long long cmp, unsigned long long val) {
-    unsigned long long r;
-    asm volatile("atom.shared.cas.b64 %0, [%1], %2, %3;" : "=l"(r) : "r"(a), "l"(cmp), "l"(val) : "memory");
-    return r;
-}
-LC_D void mbar_init(uint32_t bar, uint32_t count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory"); }
-LC_D void mbar_arrive(uint32_t bar) {
-    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar) : "memory");
-}
-LC_D void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(bar), "r"(bytes) : "memory");
-}
-LC_D void mbar_wait(uint32_t bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "LAB_WAIT:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra LAB_DONE;\n\t"
-        "bra LAB_WAIT;\n\t"
-        "LAB_DONE:\n\t}" ::"r"(bar), "r"(parity) : "memory");
-}
-// bulk asynchronous copy global -> shared (TMA, 1-D); src and dst 16-byte aligned, bytes a multiple of 16
-LC_D void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-LC_D void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-
-LC_D uint32_t prmt(uint32_t a, uint32_t b, uint32_t s) {
-    uint32_t r;
-    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(s));
-    return r;
-}
 LC_D void cas128(Slot *s, uint64_t n0, uint64_t n1, uint64_t &o0, uint64_t &o1) {
     asm volatile(
         "{\n\t"

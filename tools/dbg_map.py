@@ -32,6 +32,8 @@ cases = [("word", 4, 14), ("C2", 16, 14), ("C2", 1000, 14), ("C2", 1024, 14), ("
          ("C2", 16 << 20, 20), ("C3", 64 << 20, 21), ("C2", 256 << 20, 20), ("C5", 64 << 20, 21), ("C4", 32 << 20, 22), ("C2", 1 << 30, 20), ("C3", 1 << 30, 21)]
 variants = sys.argv[1].split(",") if len(sys.argv) > 1 else ["3", "0"]
 limit = int(sys.argv[2]) if len(sys.argv) > 2 else 40
+if len(sys.argv) > 3 and sys.argv[3] == "big":
+    cases = [("C2", 16 << 20, 20), ("C2", 256 << 20, 20), ("C2", 1 << 30, 20), ("C3", 1 << 30, 21)]
 if len(sys.argv) > 3 and sys.argv[3] == "small":
     cases = [c for c in cases if c[1] <= (64 << 20)][:11]
 for v in variants:
