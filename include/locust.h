@@ -92,6 +92,12 @@ int locust_reset(locust_ctx *ctx);
  * overlap with tokenising; pinned host memory makes that copy asynchronous. */
 int locust_map(locust_ctx *ctx, const void *data, uint64_t nbytes, int where);
 
+/* Blocks until every LOCUST_HOST buffer handed to locust_map so far has been copied to the device:
+ * from then on the caller may overwrite those buffers (a reader that refills a ring of pinned
+ * chunks while earlier chunks are tokenised, as loadFile + cudaMemcpy would if they overlapped:
+ * main.cu:242-259, :403).  Tokenising itself keeps running. */
+int locust_wait_input(locust_ctx *ctx);
+
 /* PROCESS.  Replaces thrust::partition + thrust::sort with KIVComparator
  * (main.cu:411-415; KeyValue.h:20-33, :79-84): compacts the combined records
  * out of the table and sorts them by key bytes. */

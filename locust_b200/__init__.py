@@ -29,7 +29,7 @@ EXPORTS = [
     "locust_shuffle_pack_peers", "locust_partition_histogram", "locust_partition_by_range",
     "locust_result_part_bytes", "locust_result_part_pack", "locust_result_concat",
     "locust_result_header", "locust_result_adopt_slots", "locust_peer_put", "locust_partition_by_range_sum",
-    "locust_peer_barrier", "locust_shuffle_counts", "locust_exchange_free",
+    "locust_peer_barrier", "locust_shuffle_counts", "locust_exchange_free", "locust_wait_input",
     "locust_multi_create", "locust_multi_destroy", "locust_multi_wordcount", "locust_multi_wordcount_device",
     "locust_multi_context", "locust_multi_stats", "locust_multi_last_error",
 ]
@@ -72,6 +72,7 @@ def load():
     L.locust_reset.argtypes = [vp]
     L.locust_map.argtypes = [vp, vp, u64, ctypes.c_int]
     L.locust_process.argtypes = [vp]
+    L.locust_wait_input.argtypes = [vp]
     L.locust_reduce.argtypes = [vp]
     L.locust_wordcount.argtypes = [vp, vp, u64, ctypes.c_int]
     L.locust_result_host.argtypes = [vp, pp(vp), pp(vp), pp(vp), pp(vp), pp(u64)]

@@ -528,6 +528,13 @@ int locust_map(locust_ctx *c, const void *data, uint64_t nbytes, int where) {
     return LOCUST_OK;
 }
 
+int locust_wait_input(locust_ctx *c) {
+    if (!c) return LOCUST_E_ARG;
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->copy_stream));
+    return LOCUST_OK;
+}
+
 int locust_process(locust_ctx *c) {
     if (!c) return LOCUST_E_ARG;
     if (c->stage != 0) return fail(c, LOCUST_E_STATE, "locust_process called twice");

@@ -107,6 +107,84 @@ int main(int argc, char *argv[]) {
 
     FILE *f = fopen(argv[1], "rb");
     if (!f) { perror(argv[1]); return 1; }
+    if (start_line < 0 && !getenv("LOCUST_DEVICES") && !getenv("LOCUST_WHOLE_FILE")) {
+        // loadFile's role (main.cu:242-259) without holding the file: it is read in chunks into a ring of three pinned
+        // buffers, each chunk cut after its last delimiter, and while chunk k is read from disk chunk k - 1 is on its
+        // way to the GPU and being tokenised (locust_map copies and maps asynchronously).
+        const size_t CH = getenv("LOCUST_CHUNK_MIB") ? (size_t)atol(getenv("LOCUST_CHUNK_MIB")) << 20 : (size_t)64 << 20;
+        uint8_t *ring[3] = {nullptr, nullptr, nullptr};
+        for (auto &b : ring)
+            if (cudaMallocHost(reinterpret_cast<void **>(&b), CH) != cudaSuccess) {
+                fprintf(stderr, "MapReduce: no CUDA device / pinned allocation failed (this build has no CPU path)\n");
+                return 1;
+            }
+        locust_ctx *ctx = nullptr;
+        int rc = locust_create(&cfg, &ctx);
+        if (rc) return die(ctx, "locust_create", rc);
+        bool isd[256] = {};
+        for (const char *q = " ,.-;:'()\"\t\n"; *q; ++q) isd[(uint8_t)*q] = true;
+        long nlines = 0;
+        size_t carry = 0;
+        bool last_byte_nl = true, any = false;
+        for (int k = 0;; ++k) {
+            uint8_t *b = ring[k % 3];
+            const size_t got = fread(b + carry, 1, CH - carry, f);
+            const size_t total = carry + got;
+            const bool eof = got < CH - carry;
+            size_t end = total;
+            if (!eof) {
+                while (end > 0 && !isd[b[end - 1]]) --end;
+                if (end == 0) { fprintf(stderr, "MapReduce: a token longer than the read chunk; set LOCUST_WHOLE_FILE=1\n"); return 1; }
+            }
+            if (end && memchr(b, 0, end)) {
+                fprintf(stderr, "MapReduce: input contains NUL bytes; the reference stops a line at NUL, this build refuses\n");
+                return 1;
+            }
+            for (const uint8_t *q = b, *e = b + end; q < e;) {
+                const void *nl = memchr(q, '\n', (size_t)(e - q));
+                if (!nl) break;
+                ++nlines;
+                q = (const uint8_t *)nl + 1;
+            }
+            if (end) { last_byte_nl = b[end - 1] == '\n'; any = true; }
+            rc = locust_wait_input(ctx);                 // chunk k - 1 has left its buffer: buffer (k + 1) % 3 is free
+            if (rc) return die(ctx, "locust_wait_input", rc);
+            if (end) { rc = locust_map(ctx, b, end, LOCUST_HOST); if (rc) return die(ctx, "locust_map", rc); }
+            carry = total - end;
+            if (carry) memcpy(ring[(k + 1) % 3], b + end, carry);
+            if (eof) break;
+        }
+        fclose(f);
+        if (any && !last_byte_nl) ++nlines;              // getline counts a last line without a newline
+        printf("Length: %i\n", (int)nlines);
+        rc = locust_process(ctx);
+        if (rc) return die(ctx, "locust_process", rc);
+        rc = locust_reduce(ctx);
+        if (rc) return die(ctx, "locust_reduce", rc);
+        printf("GPU mapping %d nanoseconds \n", (int)(locust_stage_ms(ctx, LOCUST_STAGE_MAP) * 1e6f));
+        printf("GPU stream compaction and sorting %d nanoseconds \n", (int)(locust_stage_ms(ctx, LOCUST_STAGE_PROCESS) * 1e6f));
+        const char *text = nullptr;
+        uint64_t nbytes = 0;
+        if (stage == 1) {
+            rc = locust_format_result(ctx, LOCUST_FORMAT_INTERMEDIATE, &text, &nbytes);
+            if (rc) return die(ctx, "locust_format_result", rc);
+            FILE *g = fopen(inter_path, "wb");
+            if (!g) { perror(inter_path); return 1; }
+            fwrite(text, 1, nbytes, g);
+            fclose(g);
+            locust_destroy(ctx);
+            printf("MODE_MULTI: Finished map\n");
+            return 0;
+        }
+        printf("GPU reduce %d nanoseconds \n", (int)(locust_stage_ms(ctx, LOCUST_STAGE_REDUCE) * 1e6f));
+        rc = locust_format_result(ctx, key_format, &text, &nbytes);
+        if (rc) return die(ctx, "locust_format_result", rc);
+        fwrite(text, 1, nbytes, stdout);
+        locust_destroy(ctx);
+        for (auto &b : ring) cudaFreeHost(b);
+        printf("\nDone\n");
+        return 0;
+    }
     fseek(f, 0, SEEK_END);
     const long sz = ftell(f);
     fseek(f, 0, SEEK_SET);

@@ -444,3 +444,20 @@ def test_streaming_map_kernel_variants(lb):
     lines = [l for l in out.splitlines() if l.startswith("variant")]
     assert len(lines) >= 16, out
     assert all(": ok " in l for l in lines), out
+
+
+def test_cli_reads_the_file_in_chunks(lb, tmp_path):
+    """single mode reads the file through a ring of pinned chunks (disk read of chunk k overlapping copy + map of
+    chunk k - 1); the stdout must not depend on the chunk size, nor differ from the whole-file path"""
+    from locust_b200.textgen import TextGen
+    exe = os.path.join(ROOT, "locust_b200", "MapReduce")
+    data = bytes(TextGen.config("C2", total_bytes=5 << 20).host(5 << 20))[:-3] + b"tail"       # no newline at the end
+    path = tmp_path / "five_mib.txt"
+    path.write_bytes(data)
+    env = dict(os.environ, LOCUST_FORMAT="cpu")
+    keep = lambda out: [l for l in out.split(b"\n") if l.startswith(b"print key: ") or l.startswith(b"Length")]
+    whole = keep(subprocess.run([exe, str(path)], env=dict(env, LOCUST_WHOLE_FILE="1"), capture_output=True, check=True).stdout)
+    for mib in ("1", "2", "64"):
+        got = keep(subprocess.run([exe, str(path)], env=dict(env, LOCUST_CHUNK_MIB=mib), capture_output=True, check=True).stdout)
+        assert got == whole, "chunk size %s MiB" % mib
+    assert len(whole) > 1000 and whole[0].startswith(b"Length: ")
