@@ -286,6 +286,7 @@ def main():
                     help="N>1: 'torchrun' = one process per GPU (the contract's launch); 'c' = this one process drives all "
                          "GPUs through locust_multi_* (the C entry point a host program would call)")
     ap.add_argument("--time-budget", type=float, default=600.0, help="seconds after which optional extras are skipped")
+    ap.add_argument("--other-gib", type=float, default=8.0, help="total size of each of the other_configs (8 = as BASELINE.json states)")
     ap.add_argument("--final", default="ordered", choices=["ordered", "gather"],
                     help="N>1: 'ordered' = parts are key ranges, every rank sorts its range, rank 0 concatenates the "
                          "slices; 'gather' = hash parts, then everything is sent to rank 0 and sorted there")
@@ -574,7 +575,7 @@ def main():
                 if rank == 0:
                     other.append({"config": cname, "skipped": "time budget of %.0f s used up" % args.time_budget})
                 continue
-            o = run_config(cname, 1 << 33, world, rank, dev, stream, args.final, args.shuffle)
+            o = run_config(cname, int(args.other_gib * (1 << 30)), world, rank, dev, stream, args.final, args.shuffle)
             if rank == 0:
                 other.append(o)
 
