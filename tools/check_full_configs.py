@@ -46,12 +46,23 @@ def run_config(name, total, world, rank, dev, stream, final="ordered", shuffle="
             tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
             res = wc.result_arrays()
             stats = wc.stats()
+            sent = float(tmax[2])
+            if peers is not None and not peers.counted:
+                # slots sized by the table: nothing counts the records on the timed path, so count them once here
+                b = job.b
+                b.reset(); b.map(text)
+                if ordered:
+                    hist = b.histogram(); dist.all_reduce(hist); b.partition_by_range(hist, world)
+                sizes = b.shuffle_sizes(world)
+                ts = torch.tensor([float(sum(x for r, x in enumerate(sizes) if r != rank))], device=dev)
+                dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+                sent = float(ts.item())
         out = {"config": name, "n_gpus": world, "bytes": per * world, "ms_per_job": float(tmax[0]), "gbs": per * world / float(tmax[0]) / 1e6,
                "unique_keys": int(len(res[2])) if rank == 0 else None, "exchange": "peers" if peers else "nccl",
                "slots": ("counted" if peers and peers.counted else "by table size") if peers else None, "final_stage": final,
-               "shuffle_ms": float(tmax[1]), "bytes_sent_max_rank": float(tmax[2]),
-               "shuffle_gbs_per_gpu": float(tmax[2]) / float(tmax[1]) / 1e6 if float(tmax[1]) > 0 else None,
-               "shuffle_frac_of_770_gbs": float(tmax[2]) / float(tmax[1]) / 1e6 / 770.0 if float(tmax[1]) > 0 else None}
+               "shuffle_ms": float(tmax[1]), "bytes_sent_max_rank": sent,
+               "shuffle_gbs_per_gpu": sent / float(tmax[1]) / 1e6 if float(tmax[1]) > 0 else None,
+               "shuffle_frac_of_770_gbs": sent / float(tmax[1]) / 1e6 / 770.0 if float(tmax[1]) > 0 else None}
         if check:
             t0 = time.perf_counter()
             host = text.cpu().numpy()
