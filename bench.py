@@ -537,6 +537,8 @@ def main():
         tokens_per_gpu = [int(x) for x in tk.tolist()]
         sha_all = [None] * world
         dist.all_gather_object(sha_all, chunk_sha)
+        torch.cuda.synchronize()
+        dist.barrier()                    # the oracle took a different time on every rank: enter the job together
         with torch.cuda.stream(stream):
             job.run(text)
             res = wc.result_arrays()
@@ -569,6 +571,9 @@ def main():
         wc3.close()
     if world > 1 and (args.other_configs == "all" or (args.other_configs == "auto" and world == 8)):
         from tools.check_full_configs import run_config
+        if rank == 0:
+            sys.stderr.write("headline done: value %.1f GB/s, %.3f ms per step, parity ok=%s; running other_configs\n"
+                             % (value, ms / args.steps, parity["ok"]))
         del text
         torch.cuda.empty_cache()
         other = []

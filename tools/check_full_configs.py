@@ -75,6 +75,9 @@ def run_config(name, total, world, rank, dev, stream, final="ordered", shuffle="
                 if why is None and wc.stats()["tokens"] != ref[3]:
                     why = "tokens differ"
                 del single
+                torch.cuda.synchronize()
+                dist.barrier()                       # the oracle took a different time on every rank; the flag barrier of the
+                                                     # exchange gives up after five seconds, so the ranks enter the job together
                 job.run(text)
                 res = wc.result_arrays()
             okt = torch.tensor([1 if why is None else 0], dtype=torch.int64, device=dev)
