@@ -33,9 +33,10 @@ constexpr int kMapWarps = kMapThreads / 32;
 #endif
 // EXPERIMENT, off by default (LOCUST_INS = 0): of the 32 warps, kInsWarps only insert.  The tokenising warps hand
 // them their queued keys through a ring in shared memory (kXSlots batches of 32 keys, an mbarrier pair per slot), so
-// that the L2 round trips of the global table stall warps that have nothing else to do.  Correct on inputs up to
-// 256 MiB, but at 1 GiB a build with two inserting warps stopped making progress (not understood; the same hand-over
-// in map_stream_kernel.cu passes at 1 GiB), so the shipped kernel tokenises with all 32 warps.
+// that the L2 round trips of the global table stall warps that have nothing else to do.  Correct, but slower on every
+// text measured (1 GiB, one B200: C2 1.75 ms against 1.49 ms, C3 2.10 against 1.80 with two inserting warps taking one
+// batch at a time; 1.76 / 2.17 taking up to four): two warps fewer tokenise, the hand-over costs the tokenisers about
+// what the inline insert did, and eight warps per scheduler already hide most of that latency.
 constexpr int kInsWarps = LOCUST_INS;
 constexpr uint32_t kXSlots = 8;
 constexpr uint32_t oXHead = 0, oXTail = 4, oXDone = 8, oXFull = 16, oXEmpty = oXFull + 8 * kXSlots, oXCount = oXEmpty + 8 * kXSlots, oXData = 256;
