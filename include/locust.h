@@ -112,6 +112,26 @@ int locust_reduce(locust_ctx *ctx);
 /* map + process + reduce in one call (single mode, main.cu:397-468). */
 int locust_wordcount(locust_ctx *ctx, const void *data, uint64_t nbytes, int where);
 
+/* A second MapReduce job on the same machinery: PageRank over an edge list.  The reference names it as a
+ * milestone ("PageRank or similar algorithm that has more work per thread than word count", docs/PROPOSAL.md:21,
+ * README.md:6) and holds no code for it, so there is no reference interface to replace; the job is defined by
+ * oracle/pagerank_oracle.c (parity unpinned) and follows the word-count conventions:
+ *   input   one edge per line, "src dst" = the first two tokens of the line under the word-count delimiter set
+ *           (main.cu:297); lines with fewer tokens are skipped, further tokens ignored, repeated edges count;
+ *           node names have at most 16 bytes (longer: LOCUST_E_ARG)
+ *   ranks   64-bit fixed point, the whole mass is 2^48; damping_q32 = damping * 2^32 (0.85 -> 3650722201);
+ *           rank0 = 2^48 / N; per iteration rank'[v] = teleport + (D * sum over u->v of rank[u] / outdeg[u]) >> 32,
+ *           teleport = ((2^48 - (2^48 * D >> 32)) + (D * mass of nodes without out-edges >> 32)) / N.
+ *           All sums are integer, so the result is independent of their order.
+ *   result  read with locust_result_host / _device / locust_format_result: keys = node names in byte order,
+ *           counts = ranks, vals = their exclusive prefix sums.
+ * Replaces whatever job was in the context (like locust_wordcount).  Grows the table when the graph has more
+ * nodes than half its slots. */
+int locust_pagerank(locust_ctx *ctx, const void *edges, uint64_t nbytes, int where, uint32_t iterations,
+                    uint64_t damping_q32);
+/* nodes and edges of the last locust_pagerank */
+int locust_pagerank_stats(locust_ctx *ctx, uint64_t *nodes, uint64_t *edges);
+
 /* Replaces the cudaMemcpy device->host of the result (main.cu:470-472).  Pointers
  * are borrowed: valid until the next locust_reset / locust_map / locust_destroy.
  * offsets has n + 1 entries; vals may be NULL. */

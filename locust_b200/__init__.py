@@ -21,7 +21,7 @@ F_GENERIC_TOKENISER, F_NO_SMEM_COMBINER, F_WEAK_HASH, F_SORT_PATH = 1, 2, 4, 8
 
 EXPORTS = [
     "locust_version", "locust_create", "locust_destroy", "locust_reset", "locust_map",
-    "locust_process", "locust_reduce", "locust_wordcount", "locust_result_host",
+    "locust_process", "locust_reduce", "locust_wordcount", "locust_pagerank", "locust_pagerank_stats", "locust_result_host",
     "locust_result_device", "locust_format_result", "locust_stage_ms", "locust_stats",
     "locust_last_error", "locust_stream", "locust_shuffle_sizes", "locust_shuffle_pack",
     "locust_shuffle_begin_merge", "locust_shuffle_merge", "locust_count_static",
@@ -75,6 +75,8 @@ def load():
     L.locust_wait_input.argtypes = [vp]
     L.locust_reduce.argtypes = [vp]
     L.locust_wordcount.argtypes = [vp, vp, u64, ctypes.c_int]
+    L.locust_pagerank.argtypes = [vp, vp, u64, ctypes.c_int, ctypes.c_uint32, u64]
+    L.locust_pagerank_stats.argtypes = [vp, pp(u64), pp(u64)]
     L.locust_result_host.argtypes = [vp, pp(vp), pp(vp), pp(vp), pp(vp), pp(u64)]
     L.locust_result_device.argtypes = [vp, pp(vp), pp(vp), pp(vp), pp(vp), pp(u64)]
     L.locust_format_result.argtypes = [vp, ctypes.c_int, pp(vp), pp(u64)]
@@ -220,6 +222,22 @@ class WordCount:
         self._keep = [keep]                 # device inputs must outlive reduce()
         self._check(self._L.locust_wordcount(self._h, ptr, n, where), "locust_wordcount")
         return self
+
+    def pagerank(self, edges, iterations=20, damping=0.85):
+        """Second job (locust_pagerank): `edges` = text with one "src dst" pair per line.  Ranks are 64-bit
+        fixed point with a total mass of 2^48; damping may be a float or an int already scaled by 2^32.
+        Read the result with result() / result_arrays(): keys = node names, counts = ranks."""
+        d = damping if isinstance(damping, int) else int(damping * 4294967296.0)
+        ptr, n, where, keep = _ptr_of(edges)
+        self._keep = [keep]
+        self._check(self._L.locust_pagerank(self._h, ptr, n, where, int(iterations), d), "locust_pagerank")
+        return self
+
+    def pagerank_stats(self):
+        u64 = ctypes.c_uint64
+        nn, ne = u64(), u64()
+        self._check(self._L.locust_pagerank_stats(self._h, ctypes.byref(nn), ctypes.byref(ne)), "locust_pagerank_stats")
+        return {"nodes": nn.value, "edges": ne.value}
 
     # -- results ------------------------------------------------------------------
     def result(self):

@@ -17,7 +17,8 @@ constexpr uint32_t kStatusBlobFull  = 8u;   // key blob too small
 constexpr uint32_t kStatusTextFull  = 16u;  // formatted-text buffer too small
 constexpr uint32_t kStatusFarFull   = 32u;  // list of long-token positions of one MAP launch too small
 constexpr uint32_t kStatusBadPart   = 64u;  // a received part does not have the layout of a packed part
-constexpr uint32_t kStatusTieFull   = 128u; // more records with a shared 16-byte prefix than the tie arrays hold
+constexpr uint32_t kStatusTieFull   = 128u;
+constexpr uint32_t kStatusNodeLong  = 256u; // PageRank job: a node name of more than 16 bytes // more records with a shared 16-byte prefix than the tie arrays hold
 
 // One entry of the long-key list: `count` occurrences of the key at ptr[0..len), len > 16.
 // Entries are (all but) distinct keys: long_keys.cuh finds an existing entry through a hash
@@ -91,6 +92,26 @@ struct MapParams {
     Records rec;                // LOCUST_F_SORT_PATH only: every token becomes a record
 };
 
+// ---- second job: PageRank over an edge list (pagerank_kernels.cu) ----
+struct PrState {
+    unsigned long long n_nodes;     // distinct node names
+    unsigned long long n_edges;     // lines with two tokens
+    unsigned long long dangling[2]; // rank mass of the nodes without out-edges, by iteration parity
+};
+struct PrArrays {                   // one value per table slot
+    unsigned long long *rank, *contrib, *acc;
+};
+struct PrParams {
+    const uint8_t *base;            // 16-byte aligned; valid bytes are base[lo .. hi)
+    uint64_t lo, hi;
+    Slot *table;                    // Slot::count = out-degree while the job runs, the rank at its end
+    uint64_t table_mask;
+    uint2 *edges;                   // (slot of src, slot of dst)
+    uint64_t edge_cap;
+    PrState *st;
+    Counters *ctr;
+};
+
 struct SortScratch {
     uint32_t *hist;          // 16 * 256 digit histograms
     uint32_t *bases;         // 16 * 256 exclusive bases
@@ -126,6 +147,12 @@ int launch_tokenize_stream(const MapParams &p, int variant, int num_sms, cudaStr
 int launch_long_tokens(const MapParams &p, int num_sms, cudaStream_t st);
 // zeroes the long-key index if the counters say the last job used it
 int launch_long_index_clear(const Counters *ctr, uint32_t *index, uint64_t slots, int num_sms, cudaStream_t st);
+
+// PageRank job: parse the edge list into the table and the edge array; start ranks, `iterations` rounds of
+// scatter + node update, ranks stored in Slot::count at the end
+int launch_pagerank_parse(const PrParams &p, int num_sms, cudaStream_t st);
+int launch_pagerank_iterate(Slot *table, uint64_t slots, const uint2 *edges, uint64_t edge_cap, PrArrays a, PrState *state,
+                            uint32_t iterations, unsigned long long damping, int num_sms, cudaStream_t st);
 
 // PROCESS
 int launch_extract(const Slot *table, uint64_t slots, Records r, Counters *ctr, int num_sms, cudaStream_t st);

@@ -84,6 +84,12 @@ struct locust_ctx {
     uint32_t *xflag = nullptr, *h_xflag = nullptr;
     std::vector<void *> exchange_bufs;
 
+    // second job (locust_pagerank): per-slot arrays, edge list, device scalars and their pinned mirror
+    PrArrays pr{};  uint64_t pr_slots = 0;
+    uint2 *pr_edges = nullptr;  uint64_t pr_edge_cap = 0;
+    PrState *pr_state = nullptr, *h_pr_state = nullptr;
+    bool pr_done = false;           // the current result is a PageRank result
+
     cudaEvent_t ev[8]{};            // map, process, reduce, shuffle: begin/end
     bool ev_set[8]{};
     uint64_t launches = 0;
@@ -470,6 +476,8 @@ int locust_destroy(locust_ctx *c) {
     cudaFree(c->sort.hist); cudaFree(c->sort.bases); cudaFree(c->sort.tickets);
     cudaFree(c->line_off); cudaFree(c->d_text); cudaFree(c->part_dev); cudaFree(c->xflag); cudaFree(c->partmap); cudaFree(c->peer_ptrs); cudaFree(c->hist_sum);
     for (void *b : c->exchange_bufs) cudaFree(b);
+    cudaFree(c->pr.rank); cudaFree(c->pr.contrib); cudaFree(c->pr.acc); cudaFree(c->pr_edges); cudaFree(c->pr_state);
+    cudaFreeHost(c->h_pr_state);
     cudaFreeHost(c->h_xflag);
     cudaFreeHost(c->h_ctr); cudaFreeHost(c->h_blob); cudaFreeHost(c->h_offsets);
     cudaFreeHost(c->h_counts); cudaFreeHost(c->h_vals); cudaFreeHost(c->h_text);
@@ -492,6 +500,7 @@ int locust_reset(locust_ctx *c) {
     c->stage = 0;
     c->host_valid = false;
     c->partmap_n = 0;
+    c->pr_done = false;
     for (auto &b : c->ev_set) b = false;
     c->launches = 0;
     c->err.clear();
@@ -563,6 +572,91 @@ int locust_wordcount(locust_ctx *c, const void *data, uint64_t nbytes, int where
     rc = locust_process(c);
     if (rc) return rc;
     return locust_reduce(c);
+}
+
+// ---- second job: PageRank over an edge list (pagerank_kernels.cu; defined by oracle/pagerank_oracle.c) ----
+int locust_pagerank(locust_ctx *c, const void *data, uint64_t nbytes, int where, uint32_t iterations, uint64_t damping_q32) {
+    int rc = locust_reset(c);
+    if (rc) return rc;
+    if (!data && nbytes) return fail(c, LOCUST_E_ARG, "locust_pagerank: data is NULL");
+    if (where != LOCUST_HOST && where != LOCUST_DEVICE) return fail(c, LOCUST_E_ARG, "locust_pagerank: bad location");
+    if (damping_q32 > (1ull << 32)) return fail(c, LOCUST_E_ARG, "locust_pagerank: damping is Q32 and at most 2^32 (1.0)");
+    if (c->flags) return fail(c, LOCUST_E_ARG, "locust_pagerank: contexts with test flags run word count only");
+    CU(cudaSetDevice(c->device));
+    if (!c->pr_state) {
+        CU(dalloc(&c->pr_state, 1));
+        CU(cudaMallocHost(reinterpret_cast<void **>(&c->h_pr_state), sizeof(PrState)));
+    }
+    const uint8_t *dev = static_cast<const uint8_t *>(data);
+    if (nbytes && where == LOCUST_HOST) {
+        uint8_t *copy = nullptr;
+        uint64_t cap = 0;
+        CU(take_device_copy(c, nbytes + 64, &copy, &cap));
+        c->segments.push_back(Segment{copy, nbytes, copy, cap});
+        CU(cudaMemcpyAsync(copy, data, nbytes, cudaMemcpyHostToDevice, c->stream));
+        dev = copy;
+    } else if (nbytes) {
+        c->segments.push_back(Segment{dev, nbytes, nullptr, 0});
+    }
+    c->replayable = false;                      // growth below is this job's own; the word-count replay must never run
+    const uint64_t want_edges = nbytes / 4 + 1;  // an edge line has at least four bytes
+    if (want_edges > c->pr_edge_cap) {
+        cudaFree(c->pr_edges); c->pr_edges = nullptr; c->pr_edge_cap = 0;
+        CU(dalloc(&c->pr_edges, want_edges));
+        c->pr_edge_cap = want_edges;
+    }
+    for (int attempt = 0; ; ++attempt) {
+        if (c->pr_slots != c->slots) {
+            cudaFree(c->pr.rank); cudaFree(c->pr.contrib); cudaFree(c->pr.acc);
+            c->pr = PrArrays{}; c->pr_slots = 0;
+            CU(dalloc(&c->pr.rank, c->slots)); CU(dalloc(&c->pr.contrib, c->slots)); CU(dalloc(&c->pr.acc, c->slots));
+            c->pr_slots = c->slots;
+        }
+        CU(cudaEventRecord(c->ev[0], c->stream)); c->ev_set[0] = true;
+        rc = clear_job(c);
+        if (rc) return rc;
+        CU(cudaMemsetAsync(c->pr_state, 0, sizeof(PrState), c->stream));
+        PrParams p{};
+        const uintptr_t a = reinterpret_cast<uintptr_t>(dev), base = a & ~uintptr_t(15);
+        p.base = reinterpret_cast<const uint8_t *>(base);
+        p.lo = a - base; p.hi = (a - base) + nbytes;
+        p.table = c->table; p.table_mask = c->slots - 1;
+        p.edges = c->pr_edges; p.edge_cap = c->pr_edge_cap;
+        p.st = c->pr_state; p.ctr = c->ctr;
+        c->launches += (uint64_t)launch_pagerank_parse(p, c->num_sms, c->stream);
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(c->h_ctr, c->ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(c->h_pr_state, c->pr_state, sizeof(PrState), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        const uint32_t st = c->h_ctr->status;
+        if (st & kStatusNodeLong) return fail(c, LOCUST_E_ARG, "locust_pagerank: a node name has more than 16 bytes");
+        if (st & kStatusEntryFull) return fail(c, LOCUST_E_STATE, "locust_pagerank: edge list overflow");
+        // redo with a larger table when it filled up, or when it is more than half full (long probe chains)
+        if (!(st & kStatusTableFull) && c->h_pr_state->n_nodes * 2 <= c->slots) break;
+        if (attempt >= 8 || c->slots >= (1ull << 32)) return fail(c, LOCUST_E_CAPACITY, "locust_pagerank: combiner table would exceed 2^32 slots");
+        uint64_t slots = c->slots * 4;
+        while (slots < 2 * c->h_pr_state->n_nodes && slots < (1ull << 32)) slots *= 2;
+        rc = alloc_sized(c, slots, c->long_cap);
+        if (rc) return rc;
+    }
+    c->launches += (uint64_t)launch_pagerank_iterate(c->table, c->slots, c->pr_edges, c->h_pr_state->n_edges, c->pr, c->pr_state,
+                                                     iterations, damping_q32, c->num_sms, c->stream);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(c->ev[1], c->stream)); c->ev_set[1] = true;
+    rc = run_process(c);
+    if (rc) return rc;
+    rc = finish_reduce(c);
+    if (rc) return rc;
+    c->pr_done = true;
+    return LOCUST_OK;
+}
+
+int locust_pagerank_stats(locust_ctx *c, uint64_t *nodes, uint64_t *edges) {
+    if (!c) return LOCUST_E_ARG;
+    if (!c->pr_done) return fail(c, LOCUST_E_STATE, "locust_pagerank_stats: the current result is not a PageRank result");
+    if (nodes) *nodes = c->h_pr_state->n_nodes;
+    if (edges) *edges = c->h_pr_state->n_edges;
+    return LOCUST_OK;
 }
 
 int locust_result_device(locust_ctx *c, const uint8_t **key_blob, const uint64_t **key_offsets,

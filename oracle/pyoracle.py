@@ -44,6 +44,8 @@ def lib():
         L.wc_format_cpu.restype = ctypes.c_size_t
         L.wc_format_tsv.argtypes = [ctypes.POINTER(_WcResult), ctypes.c_void_p, ctypes.c_size_t]
         L.wc_format_tsv.restype = ctypes.c_size_t
+        L.pr_oracle.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_uint64, ctypes.POINTER(_WcResult)]
+        L.pr_oracle.restype = ctypes.c_int
         _lib = L
     return _lib
 
@@ -109,6 +111,23 @@ def wordcount(data, mode="sort", emits_per_line=0, formats=True):
             L.wc_format_tsv(ctypes.byref(r), b, need)
             tsv = b.raw[:need]
         return OracleResult(keys, counts, r.tokens, cpu_lines, tsv)
+    finally:
+        L.wc_result_free(ctypes.byref(r))
+
+
+def pagerank(data, iterations, damping_q32):
+    """Second job (oracle/pagerank_oracle.c): (nodes in byte order, ranks, number of edges)."""
+    L = lib()
+    ptr, n, keep = _buf_ptr(data)
+    r = _WcResult()
+    rc = L.pr_oracle(ptr, n, iterations, damping_q32, ctypes.byref(r))
+    if rc != 0:
+        raise RuntimeError("pagerank oracle failed: %d" % rc)
+    try:
+        nu = r.n
+        offs = [r.key_offsets[i] for i in range(nu + 1)]
+        blob = ctypes.string_at(r.key_blob, offs[nu]) if nu else b""
+        return [blob[offs[i]:offs[i + 1]] for i in range(nu)], [r.counts[i] for i in range(nu)], r.tokens
     finally:
         L.wc_result_free(ctypes.byref(r))
 

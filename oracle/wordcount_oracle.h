@@ -29,6 +29,11 @@ size_t wc_format_cpu(const wc_result *res, char *out, size_t cap);
 /* canonical "word\tcount\n" lines */
 size_t wc_format_tsv(const wc_result *res, char *out, size_t cap);
 
+/* Second job (oracle/pagerank_oracle.c): PageRank over "src dst" lines in 64-bit fixed point; result
+ * records are (node, rank) in key order, res->tokens = number of edges.  0 ok, 1 out of memory, 2 a node
+ * name longer than 16 bytes. */
+int pr_oracle(const uint8_t *buf, size_t n, uint32_t iterations, uint64_t damping_q32, wc_result *res);
+
 #ifdef __cplusplus
 }
 #endif
