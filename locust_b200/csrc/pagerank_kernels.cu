@@ -4,13 +4,15 @@
 // oracle/pagerank_oracle.c is the definition these kernels are checked against.
 //
 //   parse    one pass over the text: a thread owns the lines that start in its 16 bytes, takes the first two
-//            tokens, finds or adds both in the combiner table (Slot::count of the source = out-degree) and
+//            tokens, finds or adds both in the combiner table (out-degrees are counted from the edge list afterwards) and
 //            appends the edge as a pair of slot numbers.  Edges of one 4 KiB tile are placed by a block scan,
 //            so the edge list is dense and its counter sees one atomic per tile.
 //   nodes    per slot: rank, contribution = rank / out-degree, mass of the nodes without out-edges
 //   scatter  per edge: acc[dst] += contrib[src]
 //   after the last iteration the ranks are stored in Slot::count, and PROCESS + REDUCE of the word-count path
 //   put the (node, rank) records in byte order.
+#include <cstdlib>
+
 #include "kernels.cuh"
 
 namespace locust {
@@ -33,9 +35,8 @@ LC_D void pr_cas128(Slot *s, uint64_t n0, uint64_t n1, uint64_t &o0, uint64_t &o
         : "=l"(o0), "=l"(o1) : "l"(s), "l"(0ull), "l"(n0), "l"(n1) : "memory");
 }
 
-// slot of node (k0, k1), added if new; `deg` is added to its out-degree.  0xFFFFFFFF: the table is full.
-__device__ __noinline__ uint32_t pr_find_or_add(Slot *table, uint64_t table_mask, PrState *state, Counters *ctr, uint64_t k0, uint64_t k1,
-                                                 unsigned long long deg) {
+// slot of node (k0, k1), added if new.  0xFFFFFFFF: the table is full.
+__device__ __noinline__ uint32_t pr_find_or_add(Slot *table, uint64_t table_mask, Counters *ctr, uint64_t k0, uint64_t k1) {
     uint64_t slot = slot_hash32(k0, k1) & table_mask;
     const uint64_t lim = table_mask + 1ull < (uint64_t)kPrProbe ? table_mask + 1ull : (uint64_t)kPrProbe;
     for (uint64_t probe = 0; probe < lim; ++probe) {
@@ -45,13 +46,9 @@ __device__ __noinline__ uint32_t pr_find_or_add(Slot *table, uint64_t table_mask
         if (!mine && (cur.x | cur.y) == 0ull) {
             uint64_t o0, o1;
             pr_cas128(s, k0, k1, o0, o1);
-            if ((o0 | o1) == 0ull) { atomicAdd(&state->n_nodes, 1ull); mine = true; }
-            else mine = o0 == k0 && o1 == k1;
+            mine = (o0 | o1) == 0ull || (o0 == k0 && o1 == k1);
         }
-        if (mine) {
-            if (deg) atomicAdd(&s->count, deg);
-            return (uint32_t)slot;
-        }
+        if (mine) return (uint32_t)slot;
         slot = (slot + 1) & table_mask;
     }
     atomicOr(&ctr->status, kStatusTableFull);
@@ -116,8 +113,8 @@ __global__ void __launch_bounds__(256) pr_parse_kernel(PrParams p) {
             starts &= starts - 1u;
             uint64_t key[4];
             if (!pr_parse_line(p, c + j, key)) continue;
-            const uint32_t s = pr_find_or_add(p.table, p.table_mask, p.st, p.ctr, key[0], key[1], 1ull);
-            const uint32_t d = pr_find_or_add(p.table, p.table_mask, p.st, p.ctr, key[2], key[3], 0ull);
+            const uint32_t s = pr_find_or_add(p.table, p.table_mask, p.ctr, key[0], key[1]);
+            const uint32_t d = pr_find_or_add(p.table, p.table_mask, p.ctr, key[2], key[3]);
             if (s == 0xFFFFFFFFu || d == 0xFFFFFFFFu) continue;          // table full: the job is redone
             const uint2 e = make_uint2(s, d);
             if (nv == 0) e0 = e; else if (nv == 1) e1 = e; else if (nv == 2) e2 = e; else e3 = e;
@@ -150,6 +147,40 @@ __global__ void __launch_bounds__(256) pr_parse_kernel(PrParams p) {
             atomicOr(&p.ctr->status, kStatusEntryFull);
         }
         __syncthreads();            // warp_tot and tile_base are reused by the next tile
+    }
+}
+
+// nodes = occupied slots, counted once behind the parse (an atomic per new node would queue up on one address)
+__global__ void __launch_bounds__(256) pr_count_nodes_kernel(const Slot *__restrict__ table, uint64_t slots, PrState *st) {
+    __shared__ uint32_t warp_cnt[8];
+    uint32_t mine = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * 256u + threadIdx.x; i < slots; i += (uint64_t)gridDim.x * 256u) {
+        const ulonglong2 k = __ldcg(reinterpret_cast<const ulonglong2 *>(table + i));
+        mine += (k.x | k.y) != 0ull;
+    }
+    mine = __reduce_add_sync(kFull, mine);
+    if ((threadIdx.x & 31u) == 0) warp_cnt[threadIdx.x >> 5] = mine;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t += warp_cnt[k];
+        if (t) atomicAdd(&st->n_nodes, (unsigned long long)t);
+    }
+}
+
+// out-degrees: Slot::count of every source += its edges.  A pass of its own over the edge list rather than an
+// atomic per parsed line, so that the lanes of a warp that hold the same source send one atomic between them.
+__global__ void __launch_bounds__(256) pr_degree_kernel(const uint2 *__restrict__ edges, Slot *table, const PrState *st) {
+    const unsigned long long n = st->n_edges;
+    const unsigned long long stride = (unsigned long long)gridDim.x * 256u;
+    const unsigned long long rounds = (n + stride - 1) / stride;
+    unsigned long long i = (unsigned long long)blockIdx.x * 256u + threadIdx.x;
+    for (unsigned long long r = 0; r < rounds; ++r, i += stride) {
+        const uint32_t src = i < n ? __ldg(edges + i).x : 0xFFFFFFFFu;
+        const uint32_t m = __match_any_sync(kFull, src);
+        if ((uint32_t)__ffs((int)m) - 1u == (threadIdx.x & 31u) && src != 0xFFFFFFFFu)
+            atomicAdd(&table[src].count, (unsigned long long)__popc(m));
     }
 }
 
@@ -191,14 +222,32 @@ __global__ void __launch_bounds__(256) pr_nodes_kernel(Slot *table, uint64_t slo
     }
 }
 
-// iteration `it`: acc[dst] += contrib[src]; also empties the dangling sum the closing nodes pass will fill
+// iteration `it`: acc[dst] += contrib[src]; also empties the dangling sum the closing nodes pass will fill.
+// kGroup: lanes of a warp that hold the same destination add their contributions first (MATCH.ANY + two REDUX
+// over 24-bit halves: a contribution is below 2^48, 32 of them below 2^29 per half) and send one atomic --
+// what a graph with a few heavily linked nodes needs, where the atomics on one address queue up in L2.
+template <bool kGroup>
 __global__ void __launch_bounds__(256) pr_scatter_kernel(const uint2 *__restrict__ edges, PrArrays a, PrState *st, uint32_t it) {
     if (blockIdx.x == 0 && threadIdx.x == 0) st->dangling[(it + 1u) & 1u] = 0ull;
     const unsigned long long n = st->n_edges;
-    for (unsigned long long i = (unsigned long long)blockIdx.x * 256u + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * 256u) {
-        const uint2 e = __ldg(edges + i);
-        const unsigned long long cv = __ldcg(a.contrib + e.x);
-        if (cv) atomicAdd(a.acc + e.y, cv);
+    const unsigned long long stride = (unsigned long long)gridDim.x * 256u;
+    const unsigned long long rounds = (n + stride - 1) / stride;
+    unsigned long long i = (unsigned long long)blockIdx.x * 256u + threadIdx.x;
+    for (unsigned long long r = 0; r < rounds; ++r, i += stride) {
+        uint2 e = make_uint2(0u, 0xFFFFFFFFu);
+        unsigned long long cv = 0;
+        if (i < n) {
+            e = __ldg(edges + i);
+            cv = __ldcg(a.contrib + e.x);
+        }
+        if (kGroup) {
+            const uint32_t m = __match_any_sync(kFull, e.y);
+            const uint32_t lo = __reduce_add_sync(m, (uint32_t)cv & 0xFFFFFFu);
+            const uint32_t hi = __reduce_add_sync(m, (uint32_t)(cv >> 24));
+            if ((uint32_t)__ffs((int)m) - 1u != (threadIdx.x & 31u)) continue;
+            cv = (unsigned long long)lo + ((unsigned long long)hi << 24);
+        }
+        if (cv && e.y != 0xFFFFFFFFu) atomicAdd(a.acc + e.y, cv);
     }
 }
 
@@ -209,17 +258,22 @@ int launch_pagerank_parse(const PrParams &p, int num_sms, cudaStream_t st) {
     const uint64_t tiles = (p.hi - (p.lo & ~15ull) + 4095ull) / 4096ull;
     const uint64_t want = (uint64_t)num_sms * 8u;
     pr_parse_kernel<<<(unsigned)(tiles < want ? tiles : want), 256, 0, st>>>(p);
-    return 1;
+    const uint64_t slots = p.table_mask + 1ull, blocks = (slots + 255u) / 256u;
+    pr_count_nodes_kernel<<<(unsigned)(blocks < want ? blocks : want), 256, 0, st>>>(p.table, slots, p.st);
+    return 2;
 }
 
 int launch_pagerank_iterate(Slot *table, uint64_t slots, const uint2 *edges, uint64_t edge_cap, PrArrays a, PrState *state,
                             uint32_t iterations, unsigned long long damping, int num_sms, cudaStream_t st) {
     const unsigned gn = (unsigned)((slots + 255u) / 256u < (uint64_t)num_sms * 8u ? (slots + 255u) / 256u : (uint64_t)num_sms * 8u);
     const unsigned ge = (unsigned)((edge_cap + 255u) / 256u < (uint64_t)num_sms * 8u ? (edge_cap + 255u) / 256u : (uint64_t)num_sms * 8u);
-    int launches = 1;
+    static const int group = [] { const char *e = getenv("LOCUST_PR_GROUP"); return e ? atoi(e) : 1; }();
+    int launches = 2;
+    pr_degree_kernel<<<ge ? ge : 1u, 256, 0, st>>>(edges, table, state);
     pr_nodes_kernel<<<gn, 256, 0, st>>>(table, slots, a, state, 0u, damping, iterations == 0u);
     for (uint32_t it = 0; it < iterations; ++it) {
-        pr_scatter_kernel<<<ge ? ge : 1u, 256, 0, st>>>(edges, a, state, it);
+        if (group) pr_scatter_kernel<true><<<ge ? ge : 1u, 256, 0, st>>>(edges, a, state, it);
+        else pr_scatter_kernel<false><<<ge ? ge : 1u, 256, 0, st>>>(edges, a, state, it);
         pr_nodes_kernel<<<gn, 256, 0, st>>>(table, slots, a, state, it + 1u, damping, it + 1u == iterations);
         launches += 2;
     }
