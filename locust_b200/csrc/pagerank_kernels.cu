@@ -11,8 +11,6 @@
 //   scatter  per edge: acc[dst] += contrib[src]
 //   after the last iteration the ranks are stored in Slot::count, and PROCESS + REDUCE of the word-count path
 //   put the (node, rank) records in byte order.
-#include <cstdlib>
-
 #include "kernels.cuh"
 
 namespace locust {
@@ -223,31 +221,17 @@ __global__ void __launch_bounds__(256) pr_nodes_kernel(Slot *table, uint64_t slo
 }
 
 // iteration `it`: acc[dst] += contrib[src]; also empties the dangling sum the closing nodes pass will fill.
-// kGroup: lanes of a warp that hold the same destination add their contributions first (MATCH.ANY + two REDUX
-// over 24-bit halves: a contribution is below 2^48, 32 of them below 2^29 per half) and send one atomic --
-// what a graph with a few heavily linked nodes needs, where the atomics on one address queue up in L2.
-template <bool kGroup>
+// One atomic per edge.  Letting the lanes of a warp that hold the same destination add up first (MATCH.ANY + REDUX)
+// was measured and dropped: 32 M edges over 1 M nodes took 1.40 ms per iteration instead of 0.48 ms with uniform
+// endpoints, and 1.43 instead of 1.75 ms with log-uniform ones (a few hubs), where the atomics on the hubs' addresses
+// queue up in L2 -- the match costs more than the atomics it saves (profiles/r02_pagerank.txt).
 __global__ void __launch_bounds__(256) pr_scatter_kernel(const uint2 *__restrict__ edges, PrArrays a, PrState *st, uint32_t it) {
     if (blockIdx.x == 0 && threadIdx.x == 0) st->dangling[(it + 1u) & 1u] = 0ull;
     const unsigned long long n = st->n_edges;
-    const unsigned long long stride = (unsigned long long)gridDim.x * 256u;
-    const unsigned long long rounds = (n + stride - 1) / stride;
-    unsigned long long i = (unsigned long long)blockIdx.x * 256u + threadIdx.x;
-    for (unsigned long long r = 0; r < rounds; ++r, i += stride) {
-        uint2 e = make_uint2(0u, 0xFFFFFFFFu);
-        unsigned long long cv = 0;
-        if (i < n) {
-            e = __ldg(edges + i);
-            cv = __ldcg(a.contrib + e.x);
-        }
-        if (kGroup) {
-            const uint32_t m = __match_any_sync(kFull, e.y);
-            const uint32_t lo = __reduce_add_sync(m, (uint32_t)cv & 0xFFFFFFu);
-            const uint32_t hi = __reduce_add_sync(m, (uint32_t)(cv >> 24));
-            if ((uint32_t)__ffs((int)m) - 1u != (threadIdx.x & 31u)) continue;
-            cv = (unsigned long long)lo + ((unsigned long long)hi << 24);
-        }
-        if (cv && e.y != 0xFFFFFFFFu) atomicAdd(a.acc + e.y, cv);
+    for (unsigned long long i = (unsigned long long)blockIdx.x * 256u + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * 256u) {
+        const uint2 e = __ldg(edges + i);
+        const unsigned long long cv = __ldcg(a.contrib + e.x);
+        if (cv) atomicAdd(a.acc + e.y, cv);
     }
 }
 
@@ -267,13 +251,11 @@ int launch_pagerank_iterate(Slot *table, uint64_t slots, const uint2 *edges, uin
                             uint32_t iterations, unsigned long long damping, int num_sms, cudaStream_t st) {
     const unsigned gn = (unsigned)((slots + 255u) / 256u < (uint64_t)num_sms * 8u ? (slots + 255u) / 256u : (uint64_t)num_sms * 8u);
     const unsigned ge = (unsigned)((edge_cap + 255u) / 256u < (uint64_t)num_sms * 8u ? (edge_cap + 255u) / 256u : (uint64_t)num_sms * 8u);
-    static const int group = [] { const char *e = getenv("LOCUST_PR_GROUP"); return e ? atoi(e) : 1; }();
     int launches = 2;
     pr_degree_kernel<<<ge ? ge : 1u, 256, 0, st>>>(edges, table, state);
     pr_nodes_kernel<<<gn, 256, 0, st>>>(table, slots, a, state, 0u, damping, iterations == 0u);
     for (uint32_t it = 0; it < iterations; ++it) {
-        if (group) pr_scatter_kernel<true><<<ge ? ge : 1u, 256, 0, st>>>(edges, a, state, it);
-        else pr_scatter_kernel<false><<<ge ? ge : 1u, 256, 0, st>>>(edges, a, state, it);
+        pr_scatter_kernel<<<ge ? ge : 1u, 256, 0, st>>>(edges, a, state, it);
         pr_nodes_kernel<<<gn, 256, 0, st>>>(table, slots, a, state, it + 1u, damping, it + 1u == iterations);
         launches += 2;
     }
