@@ -79,47 +79,57 @@ LC_D uint64_t long_scan(const uint8_t *s, uint64_t maxlen, uint64_t &hash) {
 // Adds `inc` occurrences of the key s[0..len) (len > 16, h = its long_hash) to the long-key list.  `s` must stay valid
 // until the job's result has been produced (it points into the input, or into a received part).
 __device__ __noinline__ static void long_insert(const MapParams &p, const uint8_t *s, uint64_t len, uint64_t h, unsigned long long inc) {
-    if (p.long_cap == 0) {                           // no room at all (locust_count_static): reported, not stored
-        atomicAdd(&p.ctr->n_long, 1ull);
-        atomicOr(&p.ctr->status, kStatusLongFull);
+    // The parameters are copied out once and the compiler is told what they point at: read through the reference
+    // inside the probe loop they would be fetched again with generic loads on every step, and the atomics would be
+    // generic ones (the function is not inlined, so it cannot see that these are global-memory pointers).
+    Counters *const ctr = p.ctr;
+    uint32_t *const index = p.long_index;
+    LongOcc *const list = p.long_list;
+    const uint64_t mask = p.long_index_mask, cap = p.long_cap;
+    __builtin_assume(__isGlobal(ctr));
+    __builtin_assume(__isGlobal(index));
+    __builtin_assume(__isGlobal(list));
+    if (cap == 0) {                                  // no room at all (locust_count_static): reported, not stored
+        atomicAdd(&ctr->n_long, 1ull);
+        atomicOr(&ctr->status, kStatusLongFull);
         return;
     }
     // a list that is already known to be too small: the host grows it and redoes the job
-    if (*reinterpret_cast<volatile uint32_t *>(&p.ctr->status) & kStatusLongFull) return;
-    uint64_t slot = h & p.long_index_mask;
-    for (uint64_t probe = 0; probe <= p.long_index_mask; ++probe, slot = (slot + 1) & p.long_index_mask) {
+    if (*reinterpret_cast<volatile uint32_t *>(&ctr->status) & kStatusLongFull) return;
+    uint64_t slot = h & mask;
+    for (uint64_t probe = 0; probe <= mask; ++probe, slot = (slot + 1) & mask) {
         // read through L2 (other SMs write these words), without an acquire: that would invalidate this SM's L1
         // on every long token.  The entry's fields are read through L2 too, at an address that depends on the
         // value read here, and the writer fences between writing the entry and publishing its position.
-        uint32_t v = __ldcg(p.long_index + slot);
+        uint32_t v = __ldcg(index + slot);
         if (v == 0u) {
-            v = atomicCAS(p.long_index + slot, 0u, kLongBusy);
+            v = atomicCAS(index + slot, 0u, kLongBusy);
             if (v == 0u) {                           // ours: make the entry, then publish its position
-                const unsigned long long idx = atomicAdd(&p.ctr->n_long, 1ull);
-                if (idx >= p.long_cap) {             // list full: the host grows it and redoes the job
-                    atomicOr(&p.ctr->status, kStatusLongFull);
+                const unsigned long long idx = atomicAdd(&ctr->n_long, 1ull);
+                if (idx >= cap) {                    // list full: the host grows it and redoes the job
+                    atomicOr(&ctr->status, kStatusLongFull);
                     return;
                 }
-                LongOcc *e = p.long_list + idx;
+                LongOcc *e = list + idx;
                 e->ptr = s; e->len = len; e->count = inc; e->hash = h;
                 __threadfence();
-                __stcg(p.long_index + slot, (uint32_t)idx + 1u);
+                __stcg(index + slot, (uint32_t)idx + 1u);
                 return;
             }
         }
         for (int spin = 0; v == kLongBusy && spin < 256; ++spin) {          // being written by its claimer: a moment
             __nanosleep(32);
-            v = __ldcg(p.long_index + slot);
+            v = __ldcg(index + slot);
         }
         if (v == kLongBusy) continue;                // still not published: cannot compare, move on (a duplicate entry at worst)
-        const ulonglong2 pl = __ldcg(reinterpret_cast<const ulonglong2 *>(p.long_list + (v - 1u)));          // ptr, len
-        const uint64_t eh = __ldcg(&p.long_list[v - 1u].hash);
+        const ulonglong2 pl = __ldcg(reinterpret_cast<const ulonglong2 *>(list + (v - 1u)));          // ptr, len
+        const uint64_t eh = __ldcg(&list[v - 1u].hash);
         if (eh == h && pl.y == len && long_equal(reinterpret_cast<const uint8_t *>(pl.x), s, len)) {
-            atomicAdd(&p.long_list[v - 1u].count, inc);
+            atomicAdd(&list[v - 1u].count, inc);
             return;
         }
     }
-    atomicOr(&p.ctr->status, kStatusLongFull);
+    atomicOr(&ctr->status, kStatusLongFull);
 }
 
 // MAP's fast kernels do not walk long tokens themselves (that needs registers and an L1 they do not have):

@@ -63,6 +63,9 @@ constexpr uint32_t kMaxProbe = 1u << 14;
 #ifndef LOCUST_SCANSTEP
 #define LOCUST_SCANSTEP 1
 #endif
+#ifndef LOCUST_LISTUNROLL
+#define LOCUST_LISTUNROLL 5        // token list: this many predicated steps, then a loop for what is left (0: loop only)
+#endif
 #ifndef LOCUST_SLOT32
 #define LOCUST_SLOT32 1
 #endif
@@ -91,17 +94,23 @@ LC_D void cas128(Slot *s, uint64_t n0, uint64_t n1, uint64_t &o0, uint64_t &o1) 
 
 // Adds `inc` occurrences of key (k0, k1) to the global table.
 // kPlain: the job runs with flags == 0, so no test switch has to be looked at.
+// Out of line, with the table handed over by value: through a reference to the kernel's parameters the function
+// would re-read table and mask with generic loads on every probe and use generic atomics (it cannot see that the
+// pointers are global memory); the inlined wrapper reads them from the constant bank at the call.
 template <bool kPlain>
-__device__ __noinline__ void global_insert(const MapParams &p, uint64_t k0, uint64_t k1, unsigned long long inc) {
+__device__ __noinline__ void global_insert_at(Slot *table, uint64_t table_mask, Counters *ctr, uint32_t flags, uint64_t k0, uint64_t k1,
+                                              unsigned long long inc) {
+    __builtin_assume(__isGlobal(table));
+    __builtin_assume(__isGlobal(ctr));
 #if LOCUST_SLOT32
     uint64_t h = slot_hash32(k0, k1);
 #else
     uint64_t h = hash_key128(k0, k1);
 #endif
-    if (!kPlain && (p.flags & LOCUST_F_WEAK_HASH)) h &= 0xFFull;
-    uint64_t slot = h & p.table_mask;
+    if (!kPlain && (flags & LOCUST_F_WEAK_HASH)) h &= 0xFFull;
+    uint64_t slot = h & table_mask;
     for (uint32_t probe = 0; probe < kMaxProbe; ++probe) {
-        Slot *s = p.table + slot;
+        Slot *s = table + slot;
         const ulonglong2 cur = __ldcg(reinterpret_cast<const ulonglong2 *>(s));
         if (cur.x == k0 && cur.y == k1) { atomicAdd(&s->count, inc); return; }
         if ((cur.x | cur.y) == 0ull) {
@@ -109,9 +118,13 @@ __device__ __noinline__ void global_insert(const MapParams &p, uint64_t k0, uint
             cas128(s, k0, k1, o0, o1);
             if ((o0 | o1) == 0ull || (o0 == k0 && o1 == k1)) { atomicAdd(&s->count, inc); return; }
         }
-        slot = (slot + 1) & p.table_mask;
+        slot = (slot + 1) & table_mask;
     }
-    atomicOr(&p.ctr->status, kStatusTableFull);
+    atomicOr(&ctr->status, kStatusTableFull);
+}
+template <bool kPlain>
+LC_D void global_insert(const MapParams &p, uint64_t k0, uint64_t k1, unsigned long long inc) {
+    global_insert_at<kPlain>(p.table, p.table_mask, p.ctr, p.flags, k0, k1, inc);
 }
 
 // Per-warp view of shared memory, kept as 32-bit offsets into the CTA's dynamic shared memory.
@@ -172,12 +185,13 @@ LC_D bool smem_hit(const WarpCtx &wc, uint32_t lo, uint32_t hi, bool probe) {
         "xor.b32 x0, k2, %1;\n\txor.b32 x1, k3, %2;\n\tor.b32 x0, x0, x1;\n\t"
         "setp.eq.and.u32 p1, x0, 0, ps;\n\t"
         "mad.lo.u32 ad, h, 8, %3;\n\t"
-        "@p0 red.shared.add.u32 [ad+%6], 1;\n\t"
-        "@p1 red.shared.add.u32 [ad+%7], 1;\n\t"
+        "selp.u32 x0, 4, 0, p1;\n\t"
+        "add.u32 ad, ad, x0;\n\t"
         "or.pred p0, p0, p1;\n\t"
+        "@p0 red.shared.add.u32 [ad+%6], 1;\n\t"          // a key sits in one way only: one atomic serves both
         "selp.u32 %0, 1, 0, p0;\n\t"
         "}"
-        : "=r"(hit) : "r"(lo), "r"(hi), "r"(wc.sb), "r"((uint32_t)probe), "n"(kBuckets), "n"(kKeysBytes), "n"(kKeysBytes + 4) : "memory");
+        : "=r"(hit) : "r"(lo), "r"(hi), "r"(wc.sb), "r"((uint32_t)probe), "n"(kBuckets), "n"(kKeysBytes) : "memory");
     return hit != 0u;
 }
 #endif
@@ -369,12 +383,35 @@ LC_D void inserter_loop(const MapParams &p, const WarpCtx &wc, uint32_t w) {
     }
 }
 
-// Phase B for one batch: lane `wc.lane` takes token number t of the row (if active).
-// All lanes call this together.
+// Tokens of more than 16 bytes, out of line: their addresses and the list's parameters are only formed here.
+// Called by the lanes that hold one (converged among themselves); they take their places in the list of far
+// tokens with one atomic between them.  Inside a function that is not inlined the compiler no longer knows that
+// the counters and the list are global memory, and would use generic atomics and stores: it is told.
 template <bool kPlain>
-LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active, uint32_t t, const uint8_t *rowp) {
-    // rowp = this lane's 16 bytes of the row; the row's byte offset is only needed for tokens longer than 16 bytes
-#define ROW_POS() ((uint64_t)(rowp - p.base) - wc.lane * 16u)
+__device__ __noinline__ void far_token(const MapParams &p, const WarpCtx &wc, uint64_t row_byte, uint32_t pos) {
+    if (kPlain) {
+        Counters *ctr = p.ctr;
+        ulonglong2 *list = p.far_list;
+        __builtin_assume(__isGlobal(ctr));
+        __builtin_assume(__isGlobal(list));
+        const uint32_t m = __activemask();
+        const uint32_t leader = (uint32_t)__ffs((int)m) - 1u;
+        unsigned long long first = 0;
+        if (wc.lane == leader) first = atomicAdd(&ctr->n_far, (unsigned long long)__popc(m));
+        first = __shfl_sync(m, first, leader);
+        const unsigned long long idx = first + __popc(m & ((1u << wc.lane) - 1u));
+        if (idx < p.far_cap)           // walked by long_tokens_kernel behind this launch
+            list[idx] = make_ulonglong2(reinterpret_cast<unsigned long long>(p.base + row_byte + pos), reinterpret_cast<unsigned long long>(p.base + p.hi));
+        else atomicOr(&ctr->status, kStatusFarFull);
+    } else {
+        token_generic<kPlain>(p, wc, row_byte + pos);
+    }
+}
+
+// Phase B for one batch: lane `wc.lane` takes token number t of the row (if active).
+// All lanes call this together.  The row is number r0 + i counted from p.base (only looked at for a token that runs on).
+template <bool kPlain, bool kAscii>
+LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool active, uint32_t t, uint64_t r0, uint32_t i) {
     const uint32_t *row32 = reinterpret_cast<const uint32_t *>(WC_ROW(wc));
     const uint32_t pos = active ? WC_DESC(wc)[t] : 0u;
     // token length: first delimiter at or after pos, within 17 bits
@@ -387,7 +424,7 @@ LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active
     const uint32_t bi = pos >> 2, o = pos & 3u;
     const uint32_t w0 = row32[bi], w1 = row32[bi + 1], w2 = row32[bi + 2], w3 = row32[bi + 3], w4 = row32[bi + 4];
     uint32_t a, b, c, d;
-    if (ascii) extract_key16_ascii(w0, w1, w2, w3, w4, o, L, a, b, c, d);      // warp-uniform branch
+    if (kAscii) extract_key16_ascii(w0, w1, w2, w3, w4, o, L, a, b, c, d);
     else extract_key16_any(w0, w1, w2, w3, w4, o, L, a, b, c, d);
     if (!kPlain && (p.flags & LOCUST_F_SORT_PATH)) {          // alternative path: one record per token, no combiner
         const uint32_t m = __ballot_sync(kFull, has);
@@ -407,7 +444,7 @@ LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active
             }
         }
         if (__any_sync(kFull, far)) {
-            if (far) token_generic<kPlain>(p, wc, ROW_POS() + pos);
+            if (far) far_token<kPlain>(p, wc, (r0 + i) * 512ull, pos);
             __syncwarp();
         }
         return;
@@ -426,13 +463,9 @@ LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool ascii, bool active
         }
     }
     if (__any_sync(kFull, far)) {
-        if (far) {
-            if (kPlain) far_push(p, ROW_POS() + pos);                 // walked by long_tokens_kernel behind this launch
-            else token_generic<kPlain>(p, wc, ROW_POS() + pos);
-        }
+        if (far) far_token<kPlain>(p, wc, (r0 + i) * 512ull, pos);
         __syncwarp();
     }
-#undef ROW_POS
 }
 
 template <bool kPlain>
@@ -500,21 +533,25 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
         };
         uint4 c = load_row(0u);
         uint4 n = load_row(1u);
+        // inside the loop only rows 2.. are loaded, and the one row that can start before lo is row 0 or 1 (f0 <= 1):
+        // one bound is enough there
+        const uint32_t f_end = f0 + flen;
+        // dc carries two rows' masks: this row's in the low half, the previous row's above it (only the top bit of
+        // lane 31's is ever looked at: the byte in front of the row) -- one register instead of two
         uint32_t dc = classify16_bal<kImadAdds>(c.x, c.y, c.z, c.w, one);
         uint32_t dn = classify16_bal<kImadAdds>(n.x, n.y, n.z, n.w, one);
         bool asc_c = !__any_sync(kFull, (c.x | c.y | c.z | c.w) & 0x80808080u);
         bool asc_n = !__any_sync(kFull, (n.x | n.y | n.z | n.w) & 0x80808080u);
-        // mask of the chunk in front of lane 0; only its top bit (last byte) is used
-        uint32_t pd;
         {
             const uint64_t b = r0 * 512ull;
-            pd = (b <= p.lo || is_delim(p.base[b - 1])) ? 0x8000u : 0u;
+            dc |= (b <= p.lo || is_delim(p.base[b - 1])) ? 0x80000000u : 0u;
         }
         for (uint32_t i = 0; i < n_rows; ++i) {
-            const uint4 nn = load_row(i + 2u);                             // in flight while this row is tokenised
-            const uint32_t d_dn = __shfl_sync(kFull, lane == 31 ? pd : dc, (lane + 31) & 31);
-            uint32_t starts = ~dc & ((dc << 1) | (d_dn >> 15)) & 0xFFFFu;
-            const uint8_t *rowp = q + (uint64_t)i * 512ull;
+            // in flight while this row is tokenised
+            const uint4 nn = i + 2u < f_end ? ldg_stream(q + (uint64_t)(i + 2u) * 512ull) : load_chunk(p, r0 + (uint64_t)(i + 2u), lane);
+            // mask of the chunk in front (the source lane is taken modulo 32: lane 0 hears from lane 31)
+            const uint32_t d_dn = __shfl_sync(kFull, lane == 31 ? dc >> 16 : dc, lane - 1u);
+            uint32_t starts = ~dc & ((dc << 1) | ((d_dn >> 15) & 1u)) & 0xFFFFu;
             if (use_fast) {
                 // A: stage bytes and delimiter bits (with the next row's first chunks as look-ahead)
                 reinterpret_cast<uint4 *>(WC_ROW(wc))[lane] = c;
@@ -536,26 +573,46 @@ __global__ void __launch_bounds__(kMapThreads, 1) tokenize_combine_kernel(const 
 #endif
                 const uint32_t total = __shfl_sync(kFull, incl, 31);
                 uint32_t at = incl;                                         // filled from the back: order within a row is free
+#if LOCUST_LISTUNROLL > 0
+                {
+                    // predicated steps instead of a loop whose trip count differs from lane to lane
+                    const uint32_t dl = (uint32_t)__cvta_generic_to_shared(WC_DESC(wc)) + 2u * incl;
+                    const uint32_t l16 = lane * 16u;
+#pragma unroll
+                    for (int k = 0; k < LOCUST_LISTUNROLL; ++k) {
+                        uint32_t top;
+                        asm("bfind.u32 %0, %1;" : "=r"(top) : "r"(starts));
+                        if (starts) sts16(dl - 2u * (uint32_t)(k + 1), l16 + top);
+                        starts ^= shl_clamp(1u, top);              // top = 0xFFFFFFFF when nothing is left: no bit
+                    }
+                    at -= LOCUST_LISTUNROLL;
+                }
+                if (__any_sync(kFull, starts != 0u))
+#endif
                 while (starts) {
                     const uint32_t top = 31u - (uint32_t)__clz((int)starts);
                     WC_DESC(wc)[--at] = (uint16_t)(lane * 16u + top);
                     starts ^= 1u << top;
                 }
                 __syncwarp();
-                // B: one token per lane, 32 at a time
-                const bool ascii = asc_c && asc_n;
+                // B: one token per lane, 32 at a time; the text is pure ASCII or not for a whole row: two loops
+                if (asc_c && asc_n) {
 #pragma unroll 1
-                for (uint32_t t0 = 0; t0 < total; t0 += 32) process_batch<kPlain>(p, wc, ascii, t0 + lane < total, t0 + lane, rowp);
+                    for (uint32_t t0 = 0; t0 < total; t0 += 32) process_batch<kPlain, true>(p, wc, t0 + lane < total, t0 + lane, r0, i);
+                } else {
+#pragma unroll 1
+                    for (uint32_t t0 = 0; t0 < total; t0 += 32) process_batch<kPlain, false>(p, wc, t0 + lane < total, t0 + lane, r0, i);
+                }
                 __syncwarp();
             } else {
                 while (starts) {
                     const uint32_t pp = (uint32_t)__ffs((int)starts) - 1u;
                     starts &= starts - 1u;
-                    token_generic<kPlain>(p, wc, (uint64_t)(rowp - p.base) + pp);
+                    token_generic<kPlain>(p, wc, (r0 + i) * 512ull + lane * 16u + pp);
                 }
                 __syncwarp();
             }
-            pd = dc; c = n; dc = dn; asc_c = asc_n;
+            c = n; dc = (dc << 16) | dn; asc_c = asc_n;
             n = nn;
             dn = classify16_bal<kImadAdds>(n.x, n.y, n.z, n.w, one);
             asc_n = !__any_sync(kFull, (n.x | n.y | n.z | n.w) & 0x80808080u);
