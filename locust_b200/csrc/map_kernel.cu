@@ -462,10 +462,7 @@ LC_D void process_batch(const MapParams &p, WarpCtx &wc, bool active, uint32_t t
             else drain_queue<kPlain>(p, wc, 32u);
         }
     }
-    if (__any_sync(kFull, far)) {
-        if (far) far_token<kPlain>(p, wc, (r0 + i) * 512ull, pos);
-        __syncwarp();
-    }
+    if (far) far_token<kPlain>(p, wc, (r0 + i) * 512ull, pos);       // rare; nothing the other lanes have to wait for
 }
 
 template <bool kPlain>

@@ -24,11 +24,11 @@ FUNC_PHASE = {  # device function -> phase
     "process_batch": "B token: extract + probe", "smem_hit": "B token: extract + probe", "smem_bucket": "B token: extract + probe",
     "take_token": "B token: extract + probe", "extract_key16_ascii": "B token: extract + probe", "extract_key16_any": "B token: extract + probe",
     "key_selectors": "B token: extract + probe", "byte_perm": "B token: extract + probe", "shl_clamp": "B token: extract + probe",
-    "drain_queue": "drain / insert (global table)", "global_insert": "drain / insert (global table)", "smem_insert": "drain / insert (global table)",
+    "drain_queue": "drain / insert (global table)", "global_insert": "drain / insert (global table)", "global_insert_at": "drain / insert (global table)", "smem_insert": "drain / insert (global table)",
     "insert_batches": "drain / insert (global table)", "insert_keys": "drain / insert (global table)", "global_probe": "drain / insert (global table)",
     "insert": "drain / insert (global table)", "hash_key128": "drain / insert (global table)", "mix64": "drain / insert (global table)",
     "slot_hash32": "drain / insert (global table)", "cas128": "drain / insert (global table)", "hand_over": "hand-over to inserter warps",
-    "far_push": "long tokens", "long_insert": "long tokens", "token_generic": "long tokens",
+    "far_push": "long tokens", "far_token": "long tokens", "long_insert": "long tokens", "token_generic": "long tokens",
 }
 def func_of(f, ln):
     lines = SRC.get(f)
