@@ -152,7 +152,7 @@ LC_D uint32_t smem_bucket(uint32_t lo, uint32_t hi) {
 // a divergent branch.  A miss is queued by the caller; the queue's drain claims free ways.
 // Branch free, on 32-bit shared addresses (wc.sb = the CTA's shared window, kept in a register: the
 // generic-pointer form recomputed it from a special register for every batch): a predicated 128-bit load of
-// the bucket, two compares, two predicated atomics.  `probe` says whether this lane has a key of <= 8 bytes.
+// the bucket, two compares, one predicated atomic (a key sits in one way only).  `probe` says whether this lane has a key of <= 8 bytes.
 #ifndef LOCUST_ASM_PROBE
 #define LOCUST_ASM_PROBE 1
 #endif
