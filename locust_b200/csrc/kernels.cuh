@@ -97,6 +97,7 @@ struct PrState {
     unsigned long long n_nodes;     // distinct node names
     unsigned long long n_edges;     // lines with two tokens
     unsigned long long dangling[2]; // rank mass of the nodes without out-edges, by iteration parity
+    unsigned long long n_hot;       // edges into heavily linked nodes (marked in the edge list)
 };
 struct PrArrays {                   // one value per table slot
     unsigned long long *rank, *contrib, *acc;
@@ -106,7 +107,7 @@ struct PrParams {
     uint64_t lo, hi;
     Slot *table;                    // Slot::count = out-degree while the job runs, the rank at its end
     uint64_t table_mask;
-    uint2 *edges;                   // (slot of src, slot of dst)
+    uint2 *edges;                   // (slot of src, slot of dst; top bit of dst: a heavily linked node, set after the parse)
     uint64_t edge_cap;
     PrState *st;
     Counters *ctr;
@@ -151,7 +152,7 @@ int launch_long_index_clear(const Counters *ctr, uint32_t *index, uint64_t slots
 // PageRank job: parse the edge list into the table and the edge array; start ranks, `iterations` rounds of
 // scatter + node update, ranks stored in Slot::count at the end
 int launch_pagerank_parse(const PrParams &p, int num_sms, cudaStream_t st);
-int launch_pagerank_iterate(Slot *table, uint64_t slots, const uint2 *edges, uint64_t edge_cap, PrArrays a, PrState *state,
+int launch_pagerank_iterate(Slot *table, uint64_t slots, uint2 *edges, uint64_t edge_cap, PrArrays a, PrState *state,
                             uint32_t iterations, unsigned long long damping, int num_sms, cudaStream_t st);
 
 // PROCESS

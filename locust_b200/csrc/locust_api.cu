@@ -582,6 +582,7 @@ int locust_pagerank(locust_ctx *c, const void *data, uint64_t nbytes, int where,
     if (where != LOCUST_HOST && where != LOCUST_DEVICE) return fail(c, LOCUST_E_ARG, "locust_pagerank: bad location");
     if (damping_q32 > (1ull << 32)) return fail(c, LOCUST_E_ARG, "locust_pagerank: damping is Q32 and at most 2^32 (1.0)");
     if (c->flags) return fail(c, LOCUST_E_ARG, "locust_pagerank: contexts with test flags run word count only");
+    if (c->slots > (1ull << 31)) return fail(c, LOCUST_E_ARG, "locust_pagerank: needs a table of at most 2^31 slots (edges carry slot numbers in 31 bits)");
     CU(cudaSetDevice(c->device));
     if (!c->pr_state) {
         CU(dalloc(&c->pr_state, 1));
@@ -633,12 +634,14 @@ int locust_pagerank(locust_ctx *c, const void *data, uint64_t nbytes, int where,
         if (st & kStatusEntryFull) return fail(c, LOCUST_E_STATE, "locust_pagerank: edge list overflow");
         // redo with a larger table when it filled up, or when it is more than half full (long probe chains)
         if (!(st & kStatusTableFull) && c->h_pr_state->n_nodes * 2 <= c->slots) break;
-        if (attempt >= 8 || c->slots >= (1ull << 32)) return fail(c, LOCUST_E_CAPACITY, "locust_pagerank: combiner table would exceed 2^32 slots");
+        if (attempt >= 8 || c->slots >= (1ull << 31)) return fail(c, LOCUST_E_CAPACITY, "locust_pagerank: more nodes than a table of 2^31 slots holds");
         uint64_t slots = c->slots * 4;
-        while (slots < 2 * c->h_pr_state->n_nodes && slots < (1ull << 32)) slots *= 2;
+        while (slots < 2 * c->h_pr_state->n_nodes && slots < (1ull << 31)) slots *= 2;
+        if (slots > (1ull << 31)) slots = 1ull << 31;
         rc = alloc_sized(c, slots, c->long_cap);
         if (rc) return rc;
     }
+    CU(cudaMemsetAsync(c->pr.acc, 0, c->slots * sizeof(unsigned long long), c->stream));      // counts in-degrees first
     c->launches += (uint64_t)launch_pagerank_iterate(c->table, c->slots, c->pr_edges, c->h_pr_state->n_edges, c->pr, c->pr_state,
                                                      iterations, damping_q32, c->num_sms, c->stream);
     CU(cudaGetLastError());

@@ -8,7 +8,8 @@
 //            appends the edge as a pair of slot numbers.  Edges of one 4 KiB tile are placed by a block scan,
 //            so the edge list is dense and its counter sees one atomic per tile.
 //   nodes    per slot: rank, contribution = rank / out-degree, mass of the nodes without out-edges
-//   scatter  per edge: acc[dst] += contrib[src]
+//   scatter  per edge: acc[dst] += contrib[src]; edges into heavily linked nodes are added up per block in shared
+//            memory first (their atomics would queue on one L2 address)
 //   after the last iteration the ranks are stored in Slot::count, and PROCESS + REDUCE of the word-count path
 //   put the (node, rank) records in byte order.
 #include "kernels.cuh"
@@ -167,18 +168,44 @@ __global__ void __launch_bounds__(256) pr_count_nodes_kernel(const Slot *__restr
     }
 }
 
-// out-degrees: Slot::count of every source += its edges.  A pass of its own over the edge list rather than an
-// atomic per parsed line, so that the lanes of a warp that hold the same source send one atomic between them.
-__global__ void __launch_bounds__(256) pr_degree_kernel(const uint2 *__restrict__ edges, Slot *table, const PrState *st) {
+// Degrees in one pass over the edge list.  Out-degree: Slot::count of every source += its edges (the lanes of a warp
+// that hold the same source send one atomic between them).  In-degree: counted into acc, which the first nodes pass
+// empties again; it only serves to find the heavily linked nodes.
+__global__ void __launch_bounds__(256) pr_degree_kernel(const uint2 *__restrict__ edges, Slot *table, PrArrays a, const PrState *st) {
     const unsigned long long n = st->n_edges;
     const unsigned long long stride = (unsigned long long)gridDim.x * 256u;
     const unsigned long long rounds = (n + stride - 1) / stride;
     unsigned long long i = (unsigned long long)blockIdx.x * 256u + threadIdx.x;
     for (unsigned long long r = 0; r < rounds; ++r, i += stride) {
-        const uint32_t src = i < n ? __ldg(edges + i).x : 0xFFFFFFFFu;
-        const uint32_t m = __match_any_sync(kFull, src);
-        if ((uint32_t)__ffs((int)m) - 1u == (threadIdx.x & 31u) && src != 0xFFFFFFFFu)
-            atomicAdd(&table[src].count, (unsigned long long)__popc(m));
+        uint2 e = make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);
+        if (i < n) e = __ldg(edges + i);
+        const uint32_t m = __match_any_sync(kFull, e.x);
+        if ((uint32_t)__ffs((int)m) - 1u == (threadIdx.x & 31u) && e.x != 0xFFFFFFFFu)
+            atomicAdd(&table[e.x].count, (unsigned long long)__popc(m));
+        if (e.y != 0xFFFFFFFFu) atomicAdd(a.acc + e.y, 1ull);
+    }
+}
+
+// An edge into a node with at least kHotDegree in-edges gets the top bit of its destination set: the scatter
+// passes add such edges up in shared memory before they touch the node's accumulator.
+constexpr unsigned long long kHotDegree = 8192;
+constexpr uint32_t kHotBit = 0x80000000u;
+__global__ void __launch_bounds__(256) pr_mark_hot_kernel(uint2 *edges, PrArrays a, PrState *st) {
+    __shared__ uint32_t warp_cnt[8];
+    const unsigned long long n = st->n_edges;
+    uint32_t mine = 0;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * 256u + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * 256u) {
+        const uint32_t d = edges[i].y;
+        if (__ldcg(a.acc + d) >= kHotDegree) { edges[i].y = d | kHotBit; ++mine; }
+    }
+    mine = __reduce_add_sync(kFull, mine);
+    if ((threadIdx.x & 31u) == 0) warp_cnt[threadIdx.x >> 5] = mine;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t += warp_cnt[k];
+        if (t) atomicAdd(&st->n_hot, (unsigned long long)t);
     }
 }
 
@@ -221,17 +248,61 @@ __global__ void __launch_bounds__(256) pr_nodes_kernel(Slot *table, uint64_t slo
 }
 
 // iteration `it`: acc[dst] += contrib[src]; also empties the dangling sum the closing nodes pass will fill.
-// One atomic per edge.  Letting the lanes of a warp that hold the same destination add up first (MATCH.ANY + REDUX)
-// was measured and dropped: 32 M edges over 1 M nodes took 1.40 ms per iteration instead of 0.48 ms with uniform
-// endpoints, and 1.43 instead of 1.75 ms with log-uniform ones (a few hubs), where the atomics on the hubs' addresses
-// queue up in L2 -- the match costs more than the atomics it saves (profiles/r02_pagerank.txt).
+// One atomic per edge, except for edges into heavily linked nodes (marked by pr_mark_hot_kernel): atomics on one
+// address queue up in L2 (32 M edges over 1 M nodes: 0.48 ms per iteration with uniform endpoints, 1.75 ms when a few
+// hundred nodes receive 40 % of the edges), so a block adds those up in a direct-mapped table in shared memory over
+// a chunk of 8192 edges and sends one atomic per node and chunk.  A destination that finds its place taken by another
+// node goes to global memory directly.  All sums are integer sums: the result does not depend on any of this.
+// (Letting the lanes of a warp that hold the same destination add up first -- MATCH.ANY + REDUX -- was measured and
+// dropped: 1.40 / 1.43 ms, the match costs more than the atomics it saves; profiles/r02_pagerank.txt.)
+constexpr uint32_t kHotSlots = 1024, kScatterChunk = 256 * 32;
 __global__ void __launch_bounds__(256) pr_scatter_kernel(const uint2 *__restrict__ edges, PrArrays a, PrState *st, uint32_t it) {
+    __shared__ uint32_t hkey[kHotSlots];
+    __shared__ uint32_t hval[3][kHotSlots];          // 16-bit limbs of the sums: 64-bit shared atomics are compare-and-swap loops
     if (blockIdx.x == 0 && threadIdx.x == 0) st->dangling[(it + 1u) & 1u] = 0ull;
     const unsigned long long n = st->n_edges;
-    for (unsigned long long i = (unsigned long long)blockIdx.x * 256u + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * 256u) {
-        const uint2 e = __ldg(edges + i);
-        const unsigned long long cv = __ldcg(a.contrib + e.x);
-        if (cv) atomicAdd(a.acc + e.y, cv);
+    if (st->n_hot == 0ull) {                         // no heavily linked node in this graph
+        for (unsigned long long i = (unsigned long long)blockIdx.x * 256u + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * 256u) {
+            const uint2 e = __ldg(edges + i);
+            const unsigned long long cv = __ldcg(a.contrib + e.x);
+            if (cv) atomicAdd(a.acc + e.y, cv);
+        }
+        return;
+    }
+    for (unsigned long long base = (unsigned long long)blockIdx.x * kScatterChunk; base < n; base += (unsigned long long)gridDim.x * kScatterChunk) {
+        for (uint32_t j = threadIdx.x; j < kHotSlots; j += 256u) { hkey[j] = 0xFFFFFFFFu; hval[0][j] = 0u; hval[1][j] = 0u; hval[2][j] = 0u; }
+        __syncthreads();
+#pragma unroll 4
+        for (uint32_t k = 0; k < kScatterChunk / 256u; ++k) {
+            const unsigned long long i = base + k * 256u + threadIdx.x;
+            if (i >= n) break;
+            const uint2 e = __ldg(edges + i);
+            const unsigned long long cv = __ldcg(a.contrib + e.x);
+            if (!cv) continue;
+            if (e.y & kHotBit) {
+                const uint32_t d = e.y & ~kHotBit, h = d & (kHotSlots - 1u);
+                const uint32_t old = atomicCAS(&hkey[h], 0xFFFFFFFFu, d);
+                if (old == 0xFFFFFFFFu || old == d) {
+                    // a contribution is below 2^48 and a chunk has 2^13 edges: three 16-bit limbs cannot overflow 32 bits
+                    atomicAdd(&hval[0][h], (uint32_t)cv & 0xFFFFu);
+                    atomicAdd(&hval[1][h], (uint32_t)(cv >> 16) & 0xFFFFu);
+                    atomicAdd(&hval[2][h], (uint32_t)(cv >> 32));
+                } else {
+                    atomicAdd(a.acc + d, cv);
+                }
+            } else {
+                atomicAdd(a.acc + e.y, cv);
+            }
+        }
+        __syncthreads();
+        for (uint32_t j = threadIdx.x; j < kHotSlots; j += 256u) {
+            const uint32_t d = hkey[j];
+            if (d != 0xFFFFFFFFu) {
+                const unsigned long long v = (unsigned long long)hval[0][j] + ((unsigned long long)hval[1][j] << 16) + ((unsigned long long)hval[2][j] << 32);
+                if (v) atomicAdd(a.acc + d, v);
+            }
+        }
+        __syncthreads();
     }
 }
 
@@ -247,15 +318,18 @@ int launch_pagerank_parse(const PrParams &p, int num_sms, cudaStream_t st) {
     return 2;
 }
 
-int launch_pagerank_iterate(Slot *table, uint64_t slots, const uint2 *edges, uint64_t edge_cap, PrArrays a, PrState *state,
+int launch_pagerank_iterate(Slot *table, uint64_t slots, uint2 *edges, uint64_t edge_cap, PrArrays a, PrState *state,
                             uint32_t iterations, unsigned long long damping, int num_sms, cudaStream_t st) {
     const unsigned gn = (unsigned)((slots + 255u) / 256u < (uint64_t)num_sms * 8u ? (slots + 255u) / 256u : (uint64_t)num_sms * 8u);
-    const unsigned ge = (unsigned)((edge_cap + 255u) / 256u < (uint64_t)num_sms * 8u ? (edge_cap + 255u) / 256u : (uint64_t)num_sms * 8u);
-    int launches = 2;
-    pr_degree_kernel<<<ge ? ge : 1u, 256, 0, st>>>(edges, table, state);
+    unsigned ge = (unsigned)((edge_cap + 255u) / 256u < (uint64_t)num_sms * 8u ? (edge_cap + 255u) / 256u : (uint64_t)num_sms * 8u);
+    if (ge == 0) ge = 1;
+    int launches = 3;
+    // acc is all zero here (the caller clears it): it counts in-degrees until the first nodes pass empties it again
+    pr_degree_kernel<<<ge, 256, 0, st>>>(edges, table, a, state);
+    pr_mark_hot_kernel<<<ge, 256, 0, st>>>(edges, a, state);
     pr_nodes_kernel<<<gn, 256, 0, st>>>(table, slots, a, state, 0u, damping, iterations == 0u);
     for (uint32_t it = 0; it < iterations; ++it) {
-        pr_scatter_kernel<<<ge ? ge : 1u, 256, 0, st>>>(edges, a, state, it);
+        pr_scatter_kernel<<<ge, 256, 0, st>>>(edges, a, state, it);
         pr_nodes_kernel<<<gn, 256, 0, st>>>(table, slots, a, state, it + 1u, damping, it + 1u == iterations);
         launches += 2;
     }

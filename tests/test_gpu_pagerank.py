@@ -54,6 +54,23 @@ def test_random_graphs(lb, zipf):
         check(wc, data, 3)            # the same context again: nothing of the last job is left behind
 
 
+def test_many_heavily_linked_nodes(lb):
+    """edges into nodes with >= 8192 in-edges are added up per block in a 1024-entry table in shared memory; with 60
+    such nodes some of them meet in one entry and take the direct path -- every path must give the same integers"""
+    import random
+    rng = random.Random(17)
+    lines = []
+    for h in range(60):
+        for i in range(9000 + 100 * h):
+            lines.append("s%d hub%d" % (rng.randrange(50_000), h))
+    for i in range(100_000):
+        lines.append("s%d t%d" % (rng.randrange(50_000), rng.randrange(50_000)))
+    rng.shuffle(lines)
+    data = ("\n".join(lines) + "\n").encode()
+    with lb.WordCount() as wc:
+        check(wc, data, 6)
+
+
 def test_table_grows_with_the_graph(lb):
     data = random_graph(60_000, 200_000, seed=9)
     with lb.WordCount(table_log2=12) as wc:         # 4096 slots for ~60 000 nodes
